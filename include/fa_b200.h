@@ -1,0 +1,130 @@
+/*
+ * fa_b200.h -- the C ABI of libflashattn_b200.so, part 2: the descriptor-style entry points.
+ *
+ * The flat FA2 symbols in fa_capi.h cannot express a sliding window, bottom-right causal
+ * alignment, FlashMask vectors on the varlen path, a KV cache or split-KV partials.  In the
+ * reference those live behind the setter-style handles of csrc/flashmask_v2/flash_api.h:14-266 and
+ * csrc/flash_attn_v3/flash_api.h (one getter+setter per field of csrc/flashmask_v2/flash.h:13-231).
+ * Here the same fields are one plain C struct (pointers and sizes only) that the caller fills and
+ * passes by pointer -- the cgo / ctypes / dlsym friendly form of the same contract.
+ *
+ * Error convention: identical to fa_capi.h (bool return + flash_attn_error()).
+ */
+#ifndef FA_B200_H_
+#define FA_B200_H_
+
+#include <stdint.h>
+#include <stdbool.h>
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FA_B200_ABI_VERSION 1
+
+/* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
+ * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
+typedef struct fa_b200_tensor {
+  void   *ptr;
+  int64_t batch_stride;
+  int64_t row_stride;
+  int64_t head_stride;
+} fa_b200_tensor;
+
+/* Mirrors Flash_fwd_params / Flash_bwd_params (reference: csrc/flash_attn/src/flash.h:30-168 and
+ * csrc/flashmask_v2/flash.h:13-231), with 64-bit strides throughout. */
+typedef struct fa_b200_params {
+  int32_t abi_version;            /* = FA_B200_ABI_VERSION */
+  int32_t is_bf16;                /* 1 = bf16, 0 = fp16 */
+
+  /* ---- tensors ---- */
+  fa_b200_tensor q, k, v, o;      /* o: forward output / backward input */
+  fa_b200_tensor dout, dq, dk, dv;/* backward only; dk/dv have h (expanded) heads iff dkv_expanded */
+  float *softmax_lse;             /* (b, h, seqlen_q) fp32; varlen: (b, h, max_seqlen_q) */
+  float *softmax_d;               /* bwd workspace (b, h, seqlen_q_rounded) fp32 */
+  float *dq_accum;                /* bwd workspace (b, h, seqlen_q_rounded, d_rounded) fp32 */
+  float *dkv_accum;               /* bwd GQA workspace, 2 x (b, h_k, seqlen_k_rounded, d_rounded) fp32, or NULL */
+
+  /* ---- sizes ---- */
+  int32_t b, seqlen_q, seqlen_k;  /* varlen: max_seqlen_q / max_seqlen_k */
+  int32_t h, h_k, d;
+  int32_t seqlen_q_rounded, seqlen_k_rounded, d_rounded;
+  int64_t total_q, total_k;       /* varlen: number of packed rows if known, else -1 */
+
+  /* ---- varlen / cache lengths ---- */
+  const int32_t *cu_seqlens_q;    /* (b+1) or NULL */
+  const int32_t *cu_seqlens_k;    /* (b+1) or NULL */
+  const int32_t *seqused_k;       /* (b) valid keys per batch element (kv cache), or NULL */
+  int32_t varlen_padded_input;    /* cu_seqlens give lengths, rows addressed by batch_stride */
+
+  /* ---- softmax ---- */
+  float   softmax_scale;
+  int32_t lse_empty_is_neg_inf;   /* 0: +inf for rows with no visible key (FA2 surface); 1: -inf (v2/v3) */
+
+  /* ---- masks ---- */
+  int32_t is_causal;
+  int32_t causal_bottom_right;    /* 0: top-left (flash_attn_*func, FA2 capi); 1: bottom-right (v2/v3, kvcache) */
+  int32_t window_left, window_right; /* -1 = unbounded; bottom-right aligned (csrc/flashmask_v2/mask.h:101-118) */
+  const int32_t *lt_start, *lt_end, *ut_start, *ut_end; /* FlashMask vectors (b, h_mask, seqlen_k) int32 or NULL */
+  int32_t h_mask;                 /* mask heads; q-head hq uses mask head hq / (h / h_mask) */
+  int32_t *flashmask_maxmin;      /* workspace 8 * b * h_mask * ceil(seqlen_k/64 rounded to 4) int32, or NULL */
+
+  /* ---- behaviour ---- */
+  int32_t dkv_expanded;           /* bwd: dk/dv are written per q-head (FA2 capi contract) */
+  int32_t deterministic;          /* bwd: serialise dQ accumulation */
+  int32_t force_generic;          /* testing: take the generic SIMT kernels instead of the tcgen05 ones */
+
+  /* ---- split-KV (decode) ---- */
+  int32_t num_splits;             /* 0/1 = no split */
+  float  *oaccum;                 /* (num_splits, b, seqlen_q, h, d) fp32 */
+  float  *lseaccum;               /* (num_splits, b, h, seqlen_q) fp32 */
+} fa_b200_params;
+
+/* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */
+bool fa_b200_fwd(const fa_b200_params *p, cudaStream_t stream);
+
+/* backward: dQ, dK, dV from dO, O, LSE.  Equivalent of flashmaskv2_run_mha_bwd. */
+bool fa_b200_bwd(const fa_b200_params *p, cudaStream_t stream);
+
+/* split-KV decode forward: writes oaccum/lseaccum when num_splits > 1 (then call fa_b200_fwd_combine),
+ * or o/softmax_lse directly when num_splits <= 1. */
+bool fa_b200_fwd_splitkv(const fa_b200_params *p, cudaStream_t stream);
+
+/* LSE-combine of split partials.  Equivalent of fa3_run_mha_fwd_combine
+ * (csrc/flash_attn_v3/flash_fwd_combine_kernel.h:194-478). */
+bool fa_b200_fwd_combine(const fa_b200_params *p, cudaStream_t stream);
+
+/* Split heuristic.  Equivalent of fa3_get_num_splits (csrc/flashmask_v2/heuristics.h:22-59). */
+int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seqlen_k, int head_size, int num_sm);
+
+/* Append new K/V rows into the cache at position seqused_k[b] (flash_attn_with_kvcache's k=/v= arguments;
+ * reference: csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1542 store_kv_new). */
+bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache,
+                       const int32_t *cache_seqlens, int batch, int seqlen_new, int seqlen_cache,
+                       int num_heads_k, int head_size, int is_bf16,
+                       int64_t new_batch_stride, int64_t new_row_stride, int64_t new_head_stride,
+                       int64_t cache_batch_stride, int64_t cache_row_stride, int64_t cache_head_stride,
+                       cudaStream_t stream);
+
+/* FlashMask block min/max scan (reference: csrc/flashmask_v2/flash_mask.hpp:162-245; order
+ * [lts_max, lts_min, ute_max, ute_min, lte_max, lte_min, uts_max, uts_min]). Exposed for tests. */
+bool fa_b200_flashmask_prepare(const fa_b200_params *p, int block_n, cudaStream_t stream);
+
+/* ring-attention step merge: (o, lse) <- merge((o, lse), (o_step, lse_step)) elementwise by LSE.
+ * o (rows, h, d) bf16/fp16 or fp32 per o_is_fp32; lse (h, rows)-agnostic: lse index = row * lse_row_stride + head * lse_head_stride. */
+bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse_step,
+                       int64_t rows, int heads, int head_size, int is_bf16, int o_is_fp32,
+                       int64_t lse_row_stride, int64_t lse_head_stride, cudaStream_t stream);
+
+/* Introspection for tests/bench. */
+int fa_b200_abi_version(void);
+/* which kernel family served the last call on this thread: 0 none, 1 generic SIMT, 2 tcgen05 */
+int fa_b200_last_kernel_kind(void);
+/* number of kernels launched by this library on this thread since the last reset */
+int64_t fa_b200_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA_B200_H_ */

@@ -1,0 +1,235 @@
+"""CPU oracle for the fused-attention hot path.  TEST INFRASTRUCTURE ONLY.
+
+This module is a CPU (PyTorch, fp32/fp64) restatement of what the reference's
+fused attention computes.  Only ``tests/``, ``__graft_entry__.smoke()`` and the
+``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it; the
+product package (``xhy-flash-attention_b200``) never does and has no CPU
+fallback.
+
+Parity pinning: ``attention_ref`` below follows the reference's own test oracle
+(``tests/test_flash_attn.py:111-159``) and is pinned against golden vectors
+produced by executing *that very function* (extracted with ``ast`` from the
+reference tree) on seeded inputs -- see ``tests/golden/make_golden.py`` and
+``tests/test_oracle_golden.py``.  The mask builders restate kernel-side
+semantics the reference's tests do not cover (the reference stores no golden
+vectors for them); each cites the file:line it follows.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+NEG_INF = float("-inf")
+
+
+# --------------------------------------------------------------------------- #
+# mask builders (True = masked out)                                           #
+# --------------------------------------------------------------------------- #
+def causal_mask_top_left(sq: int, sk: int) -> torch.Tensor:
+    """FA2 surface: column j is masked for row i iff j > i.
+
+    Follows tests/test_flash_attn.py:144-146 (``triu(ones(sq, sk), 1)``) and the
+    kernel rule ``col >= min(sk, row + 1)`` in csrc/flash_attn/src/softmax.h:143-178.
+    """
+    i = torch.arange(sq).view(sq, 1)
+    j = torch.arange(sk).view(1, sk)
+    return j > i
+
+
+def causal_mask_bottom_right(sq: int, sk: int) -> torch.Tensor:
+    """v2/v3 + kvcache surface: masked iff ``j >= i + 1 + sk - sq``.
+
+    Follows csrc/flashmask_v2/mask.h:85-97.
+    """
+    i = torch.arange(sq).view(sq, 1)
+    j = torch.arange(sk).view(1, sk)
+    return j > i + (sk - sq)
+
+
+def local_mask(sq: int, sk: int, window_left: int, window_right: int) -> torch.Tensor:
+    """Sliding window, bottom-right aligned: keep ``i+sk-sq-wl <= j <= i+sk-sq+wr``.
+
+    Negative window size = unbounded on that side (csrc/flashmask_v2/mask.h:101-118).
+    """
+    i = torch.arange(sq).view(sq, 1) + (sk - sq)
+    j = torch.arange(sk).view(1, sk)
+    m = torch.zeros(sq, sk, dtype=torch.bool)
+    if window_left >= 0:
+        m |= j < i - window_left
+    if window_right >= 0:
+        m |= j > i + window_right
+    return m
+
+
+def flashmask_dense(sq: int, sk: int, lt_start: torch.Tensor,
+                    lt_end: Optional[torch.Tensor] = None,
+                    ut_start: Optional[torch.Tensor] = None,
+                    ut_end: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Dense (…, sq, sk) bool mask from FlashMask column vectors (…, sk) int32.
+
+    Element rule (csrc/flashmask_v2/mainloop_fwd_sm90_tma_gmma_ws.hpp:1401-1461,
+    FA2 form csrc/flash_attn/src/softmax.h:180-298): for key column j, query row i
+    is masked iff ``lt_start[j] <= i < lt_end[j]`` or ``ut_start[j] <= i < ut_end[j]``;
+    a missing ``lt_end`` means +inf, a missing ``ut_start`` means 0, a missing
+    ``ut_end`` means "no upper band".
+    """
+    lead = lt_start.shape[:-1]
+    i = torch.arange(sq).view(*([1] * len(lead)), sq, 1)
+    lts = lt_start.long().unsqueeze(-2)
+    lte = lt_end.long().unsqueeze(-2) if lt_end is not None else None
+    m = i >= lts
+    if lte is not None:
+        m = m & (i < lte)
+    if ut_end is not None:
+        ute = ut_end.long().unsqueeze(-2)
+        u = i < ute
+        if ut_start is not None:
+            u = u & (i >= ut_start.long().unsqueeze(-2))
+        m = m | u
+    return m.expand(*lead, sq, sk)
+
+
+def document_lt_start(doc_lens: Sequence[int]) -> torch.Tensor:
+    """Causal document mask as one FlashMask vector: lt_start[j] = end of j's document."""
+    out = []
+    end = 0
+    for n in doc_lens:
+        end += int(n)
+        out.extend([end] * int(n))
+    return torch.tensor(out, dtype=torch.int32)
+
+
+# --------------------------------------------------------------------------- #
+# reference attention                                                         #
+# --------------------------------------------------------------------------- #
+def attention_ref(q, k, v, query_padding_mask=None, key_padding_mask=None, dropout_p=0.0,
+                  dropout_mask=None, causal=False, upcast=True, reorder_ops=False):
+    """Restatement of the reference test oracle, tests/test_flash_attn.py:111-159.
+
+    q (b, sq, h, d); k, v (b, sk, h_k, d).  GQA by repeating K/V heads (:135-136);
+    causal is TOP-LEFT aligned (:144-146); padded keys -> -inf (:142-143); padded
+    query rows -> zero output (:156-158).  Returns (output, attention) in q.dtype.
+    """
+    dtype_og = q.dtype
+    if upcast:
+        q, k, v = q.float(), k.float(), v.float()
+    b, sq, h, d = q.shape
+    sk, hk = k.shape[1], k.shape[2]
+    g = h // hk
+    k = k.repeat_interleave(g, dim=2)
+    v = v.repeat_interleave(g, dim=2)
+    if not reorder_ops:
+        scores = torch.einsum("bthd,bshd->bhts", q / math.sqrt(d), k)
+    else:
+        scores = torch.einsum("bthd,bshd->bhts", q, k / math.sqrt(d))
+    if key_padding_mask is not None:
+        scores.masked_fill_(~key_padding_mask.view(b, 1, 1, sk), NEG_INF)
+    if causal:
+        scores.masked_fill_(causal_mask_top_left(sq, sk).to(q.device), NEG_INF)
+    attention = torch.softmax(scores, dim=-1)
+    dropout_scaling = 1.0 / (1 - dropout_p)
+    attention_drop = attention.masked_fill(~dropout_mask, 0.0) if dropout_mask is not None else attention
+    output = torch.einsum("bhts,bshd->bthd", attention_drop, v * dropout_scaling)
+    if query_padding_mask is not None:
+        output.masked_fill_(~query_padding_mask.view(b, sq, 1, 1), 0.0)
+        attention = attention.masked_fill(~query_padding_mask.view(b, 1, sq, 1), 0.0)
+    return output.to(dtype=dtype_og), attention.to(dtype=dtype_og)
+
+
+def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_scale: Optional[float] = None,
+                         upcast: bool = True, reorder_ops: bool = False,
+                         lse_empty: float = float("inf")) -> Tuple[torch.Tensor, torch.Tensor]:
+    """General oracle: arbitrary boolean mask (broadcastable to (b, h, sq, sk); True = masked).
+
+    Returns (out (b,sq,h,d) in q.dtype, lse (b,h,sq) fp32).  Rows with every key
+    masked give out = 0 and ``lse = lse_empty``: +inf on the FA2 surface
+    (csrc/flash_attn/src/flash_fwd_kernel.h:514), -inf on the v2/v3 surface
+    (csrc/flashmask_v2/softmax.h:153).  ``lse = logsumexp(scale * q.k)`` over the
+    unmasked keys (natural log).  Same op order as ``attention_ref`` so that the
+    low-precision run (upcast=False, reorder_ops=True) is the reference's own
+    "PyTorch baseline" for the 2x-error criterion (tests/test_flash_attn.py:373-374).
+    """
+    dtype_og = q.dtype
+    if upcast:
+        q, k, v = q.float(), k.float(), v.float()
+    b, sq, h, d = q.shape
+    hk = k.shape[2]
+    g = h // hk
+    k = k.repeat_interleave(g, dim=2)
+    v = v.repeat_interleave(g, dim=2)
+    scale = (1.0 / math.sqrt(d)) if softmax_scale is None else softmax_scale
+    if not reorder_ops:
+        scores = torch.einsum("bthd,bshd->bhts", q * scale, k)
+    else:
+        scores = torch.einsum("bthd,bshd->bhts", q, k * scale)
+    if mask is not None:
+        scores = scores.masked_fill(mask.to(scores.device), NEG_INF)
+    lse = torch.logsumexp(scores.float(), dim=-1)
+    empty = torch.isinf(lse) & (lse < 0)
+    attention = torch.softmax(scores, dim=-1)
+    attention = torch.where(empty.unsqueeze(-1), torch.zeros_like(attention), attention)
+    out = torch.einsum("bhts,bshd->bthd", attention, v)
+    lse = torch.where(empty, torch.full_like(lse, lse_empty), lse)
+    return out.to(dtype_og), lse
+
+
+def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=True, reorder_ops=False):
+    """(out, lse, dq, dk, dv) by autograd through ``attention_masked_ref``.
+
+    This is how the reference's tests obtain gradients of the oracle
+    (tests/test_flash_attn.py:404-416: ``torch.autograd.grad(out_ref, (q,k,v), g)``).
+    """
+    q_ = q.detach().clone().requires_grad_(True)
+    k_ = k.detach().clone().requires_grad_(True)
+    v_ = v.detach().clone().requires_grad_(True)
+    out, lse = attention_masked_ref(q_, k_, v_, mask, softmax_scale, upcast, reorder_ops)
+    dq, dk, dv = torch.autograd.grad(out, (q_, k_, v_), dout.to(out.dtype))
+    return out.detach(), lse.detach(), dq, dk, dv
+
+
+def attention_varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, softmax_scale=None,
+                         upcast=True, reorder_ops=False, bottom_right=False):
+    """Packed (total, h, d) oracle: loop over sequences (csrc/flash_attn/src/block_info.h:12-37).
+
+    Returns (out (total_q,h,d), list of per-sequence lse (h, len_q))."""
+    outs, lses = [], []
+    nb = len(cu_seqlens_q) - 1
+    for i in range(nb):
+        qs, qe = int(cu_seqlens_q[i]), int(cu_seqlens_q[i + 1])
+        ks, ke = int(cu_seqlens_k[i]), int(cu_seqlens_k[i + 1])
+        sq, sk = qe - qs, ke - ks
+        mask = None
+        if causal:
+            mask = causal_mask_bottom_right(sq, sk) if bottom_right else causal_mask_top_left(sq, sk)
+        o, l = attention_masked_ref(q[qs:qe].unsqueeze(0), k[ks:ke].unsqueeze(0), v[ks:ke].unsqueeze(0),
+                                    mask, softmax_scale, upcast, reorder_ops)
+        outs.append(o[0])
+        lses.append(l[0])
+    return torch.cat(outs, 0), lses
+
+
+# --------------------------------------------------------------------------- #
+# split-KV combine + ring merge                                               #
+# --------------------------------------------------------------------------- #
+def combine_ref(o_partial: torch.Tensor, lse_partial: torch.Tensor):
+    """LSE-combine of split partials (csrc/flash_attn_v3/flash_fwd_combine_kernel.h:340-376,423-453).
+
+    o_partial (S, ..., d) fp32, lse_partial (S, ...) fp32 with -inf for empty splits.
+    ``lse = logsumexp_s(lse_s)``, ``o = sum_s exp(lse_s - lse) o_s``; all-empty -> o = 0, lse = -inf.
+    """
+    lse = torch.logsumexp(lse_partial, dim=0)
+    w = torch.exp(lse_partial - torch.where(torch.isinf(lse), torch.zeros_like(lse), lse))
+    w = torch.where(torch.isinf(lse_partial) & (lse_partial < 0), torch.zeros_like(w), w)
+    o = (w.unsqueeze(-1) * o_partial).sum(0)
+    return o, lse
+
+
+# --------------------------------------------------------------------------- #
+# FLOP convention (benchmarks/benchmark_flash_attention.py:27-30)             #
+# --------------------------------------------------------------------------- #
+def attention_flops(batch, seqlen_q, seqlen_k, nheads, headdim, causal, mode="fwd"):
+    assert mode in ("fwd", "bwd", "fwd_bwd")
+    f = 4 * batch * seqlen_q * seqlen_k * nheads * headdim // (2 if causal else 1)
+    return f if mode == "fwd" else (2.5 * f if mode == "bwd" else 3.5 * f)

@@ -1,0 +1,133 @@
+// common.h -- shared host/device definitions for libflashattn_b200.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/fa_b200.h"
+
+namespace fa {
+
+using Params = fa_b200_params;
+
+struct Error : public std::runtime_error {
+  explicit Error(const std::string &m) : std::runtime_error(m) {}
+};
+
+#define FA_CHECK(cond, msg)                                                              \
+  do {                                                                                   \
+    if (!(cond)) throw ::fa::Error(std::string(msg) + " [" #cond "] at " __FILE__ ":" +  \
+                                   std::to_string(__LINE__));                            \
+  } while (0)
+
+#define FA_CUDA(call)                                                                    \
+  do {                                                                                   \
+    cudaError_t e__ = (call);                                                            \
+    if (e__ != cudaSuccess)                                                              \
+      throw ::fa::Error(std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " + \
+                        #call + " at " __FILE__ ":" + std::to_string(__LINE__));         \
+  } while (0)
+
+// per-thread bookkeeping (api.cu)
+void note_launch(int kind);  // kind: 1 generic SIMT, 2 tcgen05
+int device_sm_count();
+int device_cc_major();
+
+// ---- kernel families -------------------------------------------------------------------------
+// generic SIMT kernels: any head_size % 8 == 0 up to 256, every mask kind, both dtypes.
+void generic_fwd(const Params &p, cudaStream_t s);
+void generic_bwd(const Params &p, cudaStream_t s);
+// tcgen05 / TMA / TMEM kernels (sm_100a): return false when the shape is outside their envelope.
+bool sm100_fwd_supported(const Params &p, std::string *why);
+void sm100_fwd(const Params &p, cudaStream_t s);
+bool sm100_bwd_supported(const Params &p, std::string *why);
+void sm100_bwd(const Params &p, cudaStream_t s);
+// bandwidth kernels
+void combine_fwd(const Params &p, cudaStream_t s);
+void flashmask_prepare(const Params &p, int block_n, cudaStream_t s);
+void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,
+               int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16,
+               int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s);
+void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
+               int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride, cudaStream_t s);
+
+// ---- device helpers shared by every kernel ------------------------------------------------------
+struct SeqInfo {
+  int64_t q_off, k_off;   // element offsets of row 0 (before head offset) for q-like / k-like tensors: use with strides
+  int q_row0, k_row0;     // first packed row (varlen) or 0
+  int sq, sk;             // actual lengths of this batch element
+};
+
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+#ifdef __CUDACC__
+// Restates csrc/flash_attn/src/block_info.h:12-37 (sum_s = cu_seqlens[b], actual = cu[b+1]-cu[b];
+// varlen_padded_input keeps the batch stride) plus seqused_k of csrc/flashmask_v2/seqlen.h:56-91.
+__device__ __forceinline__ void seq_bounds(const Params &p, int bi, int &q_row0, int &sq, int &k_row0, int &sk,
+                                           bool &q_batched, bool &k_batched) {
+  if (p.cu_seqlens_q) {
+    int a = p.cu_seqlens_q[bi];
+    sq = p.cu_seqlens_q[bi + 1] - a;
+    q_row0 = p.varlen_padded_input ? 0 : a;
+    q_batched = p.varlen_padded_input != 0;
+  } else {
+    sq = p.seqlen_q; q_row0 = 0; q_batched = true;
+  }
+  if (p.cu_seqlens_k) {
+    int a = p.cu_seqlens_k[bi];
+    sk = p.cu_seqlens_k[bi + 1] - a;
+    k_row0 = p.varlen_padded_input ? 0 : a;
+    k_batched = p.varlen_padded_input != 0;
+  } else {
+    sk = p.seqlen_k; k_row0 = 0; k_batched = true;
+  }
+  if (p.seqused_k) sk = p.seqused_k[bi];
+}
+
+// Element-level mask rule. TRUE = masked.
+//   seqlen tail + top-left causal : csrc/flash_attn/src/softmax.h:143-178 (col >= min(sk, row+1))
+//   bottom-right causal / local   : csrc/flashmask_v2/mask.h:85-118
+//   flashmask vectors             : csrc/flashmask_v2/mainloop_fwd_sm90_tma_gmma_ws.hpp:1401-1461
+struct MaskCtx {
+  int sq, sk, shift;      // shift = sk - sq
+  int causal, bottom_right, wl, wr;
+  const int32_t *lts, *lte, *uts, *ute;  // already offset to (batch, mask head), indexed by column
+};
+__device__ __forceinline__ bool is_masked(const MaskCtx &m, int row, int col) {
+  if (col >= m.sk) return true;
+  if (m.causal && col > row + (m.bottom_right ? m.shift : 0)) return true;
+  if (m.wl >= 0 && col < row + m.shift - m.wl) return true;
+  if (m.wr >= 0 && col > row + m.shift + m.wr) return true;
+  if (m.lts) {
+    int s = m.lts[col];
+    int e = m.lte ? m.lte[col] : 0x7fffffff;
+    if (row >= s && row < e) return true;
+    if (m.ute) {
+      int us = m.uts ? m.uts[col] : 0;
+      if (row >= us && row < m.ute[col]) return true;
+    }
+  }
+  return false;
+}
+__device__ __forceinline__ MaskCtx make_mask_ctx(const Params &p, int bi, int head, int sq, int sk) {
+  MaskCtx m;
+  m.sq = sq; m.sk = sk; m.shift = sk - sq;
+  m.causal = p.is_causal; m.bottom_right = p.causal_bottom_right;
+  m.wl = p.window_left; m.wr = p.window_right;
+  m.lts = m.lte = m.uts = m.ute = nullptr;
+  if (p.lt_start) {
+    int64_t off = ((int64_t)bi * p.h_mask + head / (p.h / p.h_mask)) * p.seqlen_k;
+    m.lts = p.lt_start + off;
+    m.lte = p.lt_end ? p.lt_end + off : nullptr;
+    m.uts = p.ut_start ? p.ut_start + off : nullptr;
+    m.ute = p.ut_end ? p.ut_end + off : nullptr;
+  }
+  return m;
+}
+#endif
+
+}  // namespace fa
