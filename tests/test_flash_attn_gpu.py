@@ -1,0 +1,136 @@
+"""GPU parity tests of the operator API against the oracle (mirrors the reference's tests/test_flash_attn.py:
+seeded randn inputs, mha/mqa/gqa, odd/unequal sequence lengths, head dims incl. non-multiples of 8, fp16/bf16,
+causal, packed variants, varlen via padding masks; outputs, LSE and gradients under the 2x rule)."""
+import math
+
+import pytest
+import torch
+
+from oracle import attention_oracle as orc
+from tests._util import check_2x, check_lse, oracle_all
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _inputs(b, sq, sk, h, hk, d, dtype, seed=0):
+    torch.manual_seed(seed)
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=dtype, requires_grad=True)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=dtype)
+    return q, k, v, g
+
+
+def _run_and_check(fa, q, k, v, g, causal, generic, mask=None, **kw):
+    out, lse, _ = fa.flash_attn_func(q, k, v, 0.0, None, causal, True, _force_generic=generic, **kw)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    sq, sk = q.shape[1], k.shape[1]
+    if mask is None and causal:
+        mask = orc.causal_mask_top_left(sq, sk).to(DEV)
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, mask)
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dk, *ref["dk"])
+    check_2x("dv", dv, *ref["dv"])
+
+
+@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [32, 59, 64, 96, 128, 160])
+@pytest.mark.parametrize("sq,sk", [(113, 203), (128, 217), (256, 512), (108, 256), (1023, 1024), (512, 256), (384, 384)])
+def test_flash_attn_output(fa, sq, sk, d, causal, dtype, generic):
+    # shapes from the reference list (tests/test_flash_attn.py:531); gqa with 6 q-heads, 2 kv-heads
+    q, k, v, g = _inputs(2, sq, sk, 6, 2, d, dtype)
+    _run_and_check(fa, q, k, v, g, causal, generic)
+
+
+@pytest.mark.parametrize("mha_type", ["mha", "mqa", "gqa"])
+@pytest.mark.parametrize("causal", [False, True])
+def test_flash_attn_head_types(fa, mha_type, causal):
+    h = 9
+    hk = {"mha": 9, "mqa": 1, "gqa": 3}[mha_type]  # tests/test_flash_attn.py:521,543
+    q, k, v, g = _inputs(4, 257, 257, h, hk, 128, torch.bfloat16)
+    _run_and_check(fa, q, k, v, g, causal, False)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [64, 128])
+def test_flash_attn_qkvpacked(fa, d, causal):
+    torch.manual_seed(0)
+    b, s, h = 3, 300, 4
+    qkv = torch.randn(b, s, 3, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16)
+    out, lse, _ = fa.flash_attn_qkvpacked_func(qkv, 0.0, None, causal, True)
+    (dqkv,) = torch.autograd.grad(out, qkv, g)
+    mask = orc.causal_mask_top_left(s, s).to(DEV) if causal else None
+    q, k, v = qkv.detach().unbind(2)
+    ref = oracle_all(q, k, v, g, mask)
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    for i, n in enumerate(("dq", "dk", "dv")):
+        check_2x(n, dqkv[:, :, i], *ref[n])
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_flash_attn_kvpacked(fa, causal):
+    torch.manual_seed(0)
+    b, sq, sk, h, hk, d = 2, 200, 333, 8, 2, 128
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    kv = torch.randn(b, sk, 2, hk, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=torch.float16)
+    out = fa.flash_attn_kvpacked_func(q, kv, 0.0, None, causal)
+    dq, dkv = torch.autograd.grad(out, (q, kv), g)
+    mask = orc.causal_mask_top_left(sq, sk).to(DEV) if causal else None
+    ref = oracle_all(q.detach(), kv.detach()[:, :, 0], kv.detach()[:, :, 1], g, mask)
+    check_2x("out", out, *ref["out"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dkv[:, :, 0], *ref["dk"])
+    check_2x("dv", dkv[:, :, 1], *ref["dv"])
+
+
+@pytest.mark.parametrize("seqlen", [1, 2, 5, 17, 128])
+@pytest.mark.parametrize("causal", [False, True])
+def test_flash_attn_bwd_overflow(fa, seqlen, causal):
+    """tests/test_flash_attn.py:835-878: tiny sequences with scaled-up inputs must not produce NaN."""
+    torch.manual_seed(0)
+    d, h = 128, 5
+    q = (torch.randn(2, seqlen, h, d, device=DEV, dtype=torch.bfloat16) * 5).requires_grad_()
+    k, v = [(torch.randn(2, seqlen, h, d, device=DEV, dtype=torch.bfloat16) * 3).requires_grad_() for _ in range(2)]
+    g = torch.randn(2, seqlen, h, d, device=DEV, dtype=torch.bfloat16)
+    out = fa.flash_attn_func(q, k, v, causal=causal)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    mask = orc.causal_mask_top_left(seqlen, seqlen).to(DEV) if causal else None
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, mask)
+    for n, got in (("out", out), ("dq", dq), ("dk", dk), ("dv", dv)):
+        assert not got.isnan().any()
+        check_2x(n, got, *ref[n], factor=5.0, atol=1e-3)  # the reference uses 5x + 1e-3 here (:875-878)
+
+
+def test_flash_attn_bwd_transpose(fa):
+    """tests/test_flash_attn.py:881-926: non-contiguous dout (a transposed view) is accepted."""
+    torch.manual_seed(0)
+    b, s, h, d = 5, 512, 2, 128
+    q, k, v = [torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True) for _ in range(3)]
+    out = fa.flash_attn_func(q, k, v, causal=True)
+    g = torch.randn(b, h, s, d, device=DEV, dtype=torch.bfloat16).transpose(1, 2)  # strides != contiguous
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, orc.causal_mask_top_left(s, s).to(DEV))
+    for n, got in (("dq", dq), ("dk", dk), ("dv", dv)):
+        check_2x(n, got, *ref[n])
+
+
+def test_flash_attn_race_condition(fa):
+    """tests/test_flash_attn.py:786-832: out/lse/dk/dv bit-identical across reruns; dq within a tight bound."""
+    torch.manual_seed(0)
+    q, k, v, g = _inputs(4, 512, 512, 4, 4, 128, torch.bfloat16)
+    out0, lse0, _ = fa.flash_attn_func(q, k, v, 0.0, None, True, True)
+    dq0, dk0, dv0 = torch.autograd.grad(out0, (q, k, v), g)
+    for _ in range(20):
+        out, lse, _ = fa.flash_attn_func(q, k, v, 0.0, None, True, True)
+        dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+        assert torch.equal(out, out0) and torch.equal(lse, lse0)
+        assert torch.equal(dk, dk0) and torch.equal(dv, dv0)
+        assert (dq - dq0).abs().max().item() <= 2 * (dq0.abs().max().item() * 2 ** -7)

@@ -1,0 +1,204 @@
+// api.cu -- the extern "C" surface of libflashattn_b200.so (include/fa_capi.h, include/fa_b200.h).
+//
+// Error convention follows the reference (csrc/capi/flash_attn.cu:45-67): every body is wrapped in
+// try/catch, the message is kept in thread-local storage and the call returns false.
+// There is no CPU path here: every entry point enqueues CUDA kernels on the caller's stream.
+#include <cstring>
+#include <memory>
+#include <mutex>
+
+#include "common.h"
+#include "../../include/fa_capi.h"
+
+namespace fa {
+
+static thread_local std::unique_ptr<char[]> tls_error;
+static thread_local int tls_last_kind = 0;
+static thread_local int64_t tls_launches = 0;
+
+void note_launch(int kind) {
+  tls_last_kind = kind;
+  ++tls_launches;
+}
+
+struct DevInfo { int sm_count; int cc_major; int cc_minor; };
+static DevInfo dev_info() {
+  // once-initialised per-device cache (the reference keeps the same kind of cache: csrc/capi/cuda_utils.cu:12-48)
+  static std::mutex mu;
+  static DevInfo cache[64];
+  static bool have[64] = {};
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> g(mu);
+  if (dev < 64 && have[dev]) return cache[dev];
+  DevInfo d;
+  FA_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+  FA_CUDA(cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+  FA_CUDA(cudaDeviceGetAttribute(&d.cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+  if (dev < 64) { cache[dev] = d; have[dev] = true; }
+  return d;
+}
+int device_sm_count() { return dev_info().sm_count; }
+int device_cc_major() { return dev_info().cc_major; }
+
+static void check_common(const Params &p) {
+  FA_CHECK(p.abi_version == FA_B200_ABI_VERSION, "fa_b200_params.abi_version mismatch");
+  FA_CHECK(p.b > 0, "batch size must be positive");
+  FA_CHECK(p.h > 0 && p.h_k > 0 && p.h % p.h_k == 0, "num_heads must be a multiple of num_heads_k");
+  FA_CHECK(p.d > 0 && p.d % 8 == 0 && p.d <= 256, "head_size must be a multiple of 8 and <= 256");
+  FA_CHECK(p.q.ptr && p.k.ptr && p.v.ptr, "q, k, v must be set");
+  FA_CHECK(device_cc_major() >= 10, "libflashattn_b200 needs a Blackwell (sm_100a) device");
+  if (p.lt_start) {
+    FA_CHECK(p.h_mask > 0 && p.h % p.h_mask == 0, "flashmask heads must divide num_heads");
+  } else {
+    FA_CHECK(!p.lt_end && !p.ut_start && !p.ut_end, "flashmask: lt_start is mandatory when any vector is given");
+  }
+}
+
+void run_fwd(const Params &p, cudaStream_t s) {
+  check_common(p);
+  FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
+  std::string why;
+  if (!p.force_generic && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
+  else generic_fwd(p, s);
+}
+
+void run_bwd(const Params &p, cudaStream_t s) {
+  check_common(p);
+  FA_CHECK(p.o.ptr && p.softmax_lse && p.dout.ptr && p.dq.ptr && p.dk.ptr && p.dv.ptr, "bwd tensors must be set");
+  FA_CHECK(p.softmax_d, "softmax_d workspace must be set");
+  std::string why;
+  if (!p.force_generic && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
+  else generic_bwd(p, s);
+}
+
+void run_splitkv(const Params &p, cudaStream_t s) {
+  check_common(p);
+  if (p.num_splits > 1) FA_CHECK(p.oaccum && p.lseaccum, "split-KV needs oaccum and lseaccum");
+  else FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
+  splitkv_fwd(p, s);
+}
+
+}  // namespace fa
+
+using fa::Params;
+
+#define FA_BEGIN try {
+#define FA_END                                                \
+  }                                                           \
+  catch (const std::exception &e) {                           \
+    flash_attn_set_error(e.what());                           \
+    return false;                                             \
+  }                                                           \
+  catch (...) {                                               \
+    flash_attn_set_error(nullptr);                            \
+    return false;                                             \
+  }                                                           \
+  return true;
+
+extern "C" {
+
+void flash_attn_set_error(const char *msg) {
+  if (msg == nullptr || *msg == '\0') msg = "unknown error";
+  size_t n = strlen(msg);
+  fa::tls_error.reset(new char[n + 1]);
+  memcpy(fa::tls_error.get(), msg, n + 1);
+}
+
+const char *flash_attn_error(void) { return fa::tls_error ? fa::tls_error.get() : ""; }
+
+int fa_b200_abi_version(void) { return FA_B200_ABI_VERSION; }
+int fa_b200_last_kernel_kind(void) { return fa::tls_last_kind; }
+int64_t fa_b200_launch_count(int reset) {
+  int64_t v = fa::tls_launches;
+  if (reset) fa::tls_launches = 0;
+  return v;
+}
+
+bool fa_b200_fwd(const fa_b200_params *p, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p != nullptr, "null params");
+  fa::run_fwd(*p, stream);
+  FA_END
+}
+
+bool fa_b200_bwd(const fa_b200_params *p, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p != nullptr, "null params");
+  fa::run_bwd(*p, stream);
+  FA_END
+}
+
+bool fa_b200_fwd_splitkv(const fa_b200_params *p, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p != nullptr, "null params");
+  fa::run_splitkv(*p, stream);
+  FA_END
+}
+
+bool fa_b200_fwd_combine(const fa_b200_params *p, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p != nullptr, "null params");
+  FA_CHECK(p->oaccum && p->lseaccum && p->o.ptr && p->softmax_lse && p->num_splits >= 1, "combine needs partials and outputs");
+  fa::combine_fwd(*p, stream);
+  FA_END
+}
+
+// Restates num_splits_heuristic (csrc/flashmask_v2/heuristics.h:22-59): smallest split count reaching
+// 85% of the best wave efficiency, no split when the grid already fills 80% of the SMs.
+int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seqlen_k, int head_size, int num_sm) {
+  const int block_n = 128, block_m = 64;
+  int num_n_blocks = (seqlen_k + block_n - 1) / block_n;
+  int num_m_blocks = (seqlen_q_packed + block_m - 1) / block_m;
+  int total_mblocks = batch * num_heads_k * num_m_blocks;
+  if (num_sm <= 0) num_sm = 148;
+  if (total_mblocks >= 0.8f * num_sm) return 1;
+  if (num_n_blocks <= 4) return 1;
+  int max_splits = 128;
+  if (max_splits > num_sm) max_splits = num_sm;
+  if (max_splits > num_n_blocks) max_splits = num_n_blocks;
+  float best = 0.f;
+  float eff[128];
+  for (int s = 1; s <= max_splits; ++s) {
+    float n_waves = float(total_mblocks * s) / num_sm;
+    float e = n_waves / ceilf(n_waves);
+    eff[s - 1] = e;
+    if (e > best) best = e;
+  }
+  for (int s = 1; s <= max_splits; ++s)
+    if (eff[s - 1] >= 0.85f * best) return s;
+  (void)head_size;
+  return 1;
+}
+
+bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache,
+                       const int32_t *cache_seqlens, int batch, int seqlen_new, int seqlen_cache,
+                       int num_heads_k, int head_size, int is_bf16,
+                       int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs,
+                       cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(k_new && v_new && k_cache && v_cache, "append_kv: null tensor");
+  FA_CHECK(head_size % 8 == 0, "append_kv: head_size must be a multiple of 8");
+  fa::append_kv(k_new, v_new, k_cache, v_cache, cache_seqlens, batch, seqlen_new, seqlen_cache, num_heads_k,
+                head_size, is_bf16, nbs, nrs, nhs, cbs, crs, chs, stream);
+  FA_END
+}
+
+bool fa_b200_flashmask_prepare(const fa_b200_params *p, int block_n, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p && p->lt_start && p->flashmask_maxmin, "flashmask_prepare needs lt_start and the maxmin workspace");
+  fa::flashmask_prepare(*p, block_n, stream);
+  FA_END
+}
+
+bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads,
+                       int head_size, int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride,
+                       cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(o && lse && o_step && lse_step, "lse_merge: null tensor");
+  fa::lse_merge(o, lse, o_step, lse_step, rows, heads, head_size, is_bf16, o_is_fp32, lse_row_stride,
+                lse_head_stride, stream);
+  FA_END
+}
+
+}  // extern "C"

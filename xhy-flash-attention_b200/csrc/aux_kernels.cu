@@ -1,0 +1,215 @@
+// aux_kernels.cu -- the HBM-bound helper kernels: split-KV LSE combine, FlashMask block min/max scan,
+// KV-cache append, ring-attention LSE merge.
+#include <climits>
+#include <math_constants.h>
+
+#include "common.h"
+
+namespace fa {
+namespace {
+
+template <typename T> __device__ __forceinline__ float to_f(T x);
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 x) { return __bfloat162float(x); }
+template <> __device__ __forceinline__ float to_f<__half>(__half x) { return __half2float(x); }
+template <> __device__ __forceinline__ float to_f<float>(float x) { return x; }
+template <typename T> __device__ __forceinline__ T from_f(float x);
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float x) { return __float2bfloat16_rn(x); }
+template <> __device__ __forceinline__ __half from_f<__half>(float x) { return __float2half_rn(x); }
+template <> __device__ __forceinline__ float from_f<float>(float x) { return x; }
+
+// ------------------------------------------------------------------------------------------------
+// LSE combine of split partials.  Restates csrc/flash_attn_v3/flash_fwd_combine_kernel.h:340-376,423-453:
+//   lse = logsumexp_s(lse_s); o = sum_s exp(lse_s - lse) * o_s; splits with lse_s = -inf contribute nothing.
+// One warp per (batch, row, head); partials oaccum (S, b, sq, h, d) fp32 / lseaccum (S, b, h, sq) fp32.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128) combine_kernel(const Params p) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int64_t item = (int64_t)blockIdx.x * 4 + warp;  // over b * sq * h
+  const int64_t n_items = (int64_t)p.b * p.seqlen_q * p.h;
+  if (item >= n_items) return;
+  const int hq = item % p.h;
+  const int row = (item / p.h) % p.seqlen_q;
+  const int bi = item / ((int64_t)p.h * p.seqlen_q);
+  const int S = p.num_splits;
+  const int64_t lse_split_stride = (int64_t)p.b * p.h * p.seqlen_q;
+  const float *lse_in = p.lseaccum + ((int64_t)bi * p.h + hq) * p.seqlen_q + row;
+  float mx = -CUDART_INF_F;
+  for (int s = lane; s < S; s += 32) mx = fmaxf(mx, lse_in[s * lse_split_stride]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f;
+  if (mx != -CUDART_INF_F)
+    for (int s = lane; s < S; s += 32) sum += __expf(lse_in[s * lse_split_stride] - mx);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const bool empty = (mx == -CUDART_INF_F);
+  const float lse = empty ? -CUDART_INF_F : mx + __logf(sum);
+  if (lane == 0)
+    p.softmax_lse[((int64_t)bi * p.h + hq) * p.seqlen_q + row] =
+        empty ? (p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F) : lse;
+  const int d = p.d;
+  const int64_t o_split_stride = (int64_t)p.b * p.seqlen_q * p.h * d;
+  const float *o_in = p.oaccum + (((int64_t)bi * p.seqlen_q + row) * p.h + hq) * (int64_t)d;
+  T *out = (T *)p.o.ptr + bi * p.o.batch_stride + (int64_t)row * p.o.row_stride + (int64_t)hq * p.o.head_stride;
+  for (int e = lane * 4; e < d; e += 128) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < S && !empty; ++s) {
+      const float ls = lse_in[s * lse_split_stride];
+      if (ls == -CUDART_INF_F) continue;
+      const float w = __expf(ls - lse);
+      const float4 v = *reinterpret_cast<const float4 *>(o_in + s * o_split_stride + e);
+      acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y);
+      acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
+    }
+    out[e] = from_f<T>(acc.x); out[e + 1] = from_f<T>(acc.y);
+    out[e + 2] = from_f<T>(acc.z); out[e + 3] = from_f<T>(acc.w);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// FlashMask block min/max scan.  Restates csrc/flashmask_v2/flash_mask.hpp:80-160,162-245:
+// eight arrays [b * h_mask][nblock_padded] in the order
+//   lts_max, lts_min, ute_max, ute_min, lte_max, lte_min, uts_max, uts_min
+// with nblock_padded = round_up(ceil(sk / block_n), 4); min starts at INT_MAX, max at 0 (ragged tails).
+// One warp per (mask row, n_block).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) flashmask_scan_kernel(const Params p, int block_n, int nblock, int nblock_pad) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int nb = blockIdx.x * 4 + warp;
+  const int bh = blockIdx.y;
+  if (nb >= nblock_pad) return;
+  const int64_t plane = (int64_t)p.b * p.h_mask * nblock_pad;
+  const int32_t *vecs[4] = {p.lt_start, p.ut_end, p.lt_end, p.ut_start};
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    if (vecs[v] == nullptr) continue;
+    const int32_t *src = vecs[v] + (int64_t)bh * p.seqlen_k;
+    int mx = 0, mn = INT_MAX;
+    if (nb < nblock) {
+      const int c1 = min(p.seqlen_k, (nb + 1) * block_n);
+      for (int c = nb * block_n + lane; c < c1; c += 32) {
+        const int x = src[c];
+        mx = max(mx, x); mn = min(mn, x);
+      }
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    if (lane == 0) {
+      p.flashmask_maxmin[(2 * v) * plane + (int64_t)bh * nblock_pad + nb] = mx;
+      p.flashmask_maxmin[(2 * v + 1) * plane + (int64_t)bh * nblock_pad + nb] = mn;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// KV-cache append: cache[b, cache_seqlens[b] + i] = new[b, i]
+// (flash_attn_with_kvcache's k=/v=; csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1542 store_kv_new)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+append_kv_kernel(const uint4 *k_new, const uint4 *v_new, uint4 *k_cache, uint4 *v_cache, const int32_t *cache_seqlens,
+                 int batch, int seqlen_new, int seqlen_cache, int h_k, int d8, int64_t nbs, int64_t nrs, int64_t nhs,
+                 int64_t cbs, int64_t crs, int64_t chs) {
+  const int64_t total = (int64_t)batch * seqlen_new * h_k * d8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = i % d8;
+    const int hh = (i / d8) % h_k;
+    const int r = (i / ((int64_t)d8 * h_k)) % seqlen_new;
+    const int bi = i / ((int64_t)d8 * h_k * seqlen_new);
+    const int dst_row = (cache_seqlens ? cache_seqlens[bi] : 0) + r;
+    if (dst_row >= seqlen_cache) continue;
+    // strides are in elements; a uint4 holds 8 elements
+    const int64_t so = (bi * nbs + (int64_t)r * nrs + (int64_t)hh * nhs) / 8 + c;
+    const int64_t dof = (bi * cbs + (int64_t)dst_row * crs + (int64_t)hh * chs) / 8 + c;
+    k_cache[dof] = k_new[so];
+    v_cache[dof] = v_new[so];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ring-attention step merge (same algebra as the combine): treats +inf and -inf LSE as "no contribution".
+// One warp per (row, head); o contiguous (rows, heads, d).
+// ------------------------------------------------------------------------------------------------
+template <typename TO, typename TS>
+__global__ void __launch_bounds__(128)
+lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int64_t rows, int heads, int d,
+                 int64_t lrs, int64_t lhs) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int64_t item = (int64_t)blockIdx.x * 4 + warp;
+  if (item >= rows * heads) return;
+  const int hh = item % heads;
+  const int64_t row = item / heads;
+  const int64_t li = row * lrs + hh * lhs;
+  const float l1 = lse[li], l2 = lse_step[li];
+  const bool e1 = isinf(l1), e2 = isinf(l2);
+  if (e2) return;  // nothing to add
+  float w1, w2, ln;
+  if (e1) { w1 = 0.f; w2 = 1.f; ln = l2; }
+  else {
+    const float mx = fmaxf(l1, l2);
+    const float s = __expf(l1 - mx) + __expf(l2 - mx);
+    ln = mx + __logf(s);
+    w1 = __expf(l1 - ln); w2 = __expf(l2 - ln);
+  }
+  TO *po = o + item * d;
+  const TS *ps = o_step + item * d;
+  for (int e = lane; e < d; e += 32) po[e] = from_f<TO>(w1 * to_f(po[e]) + w2 * to_f(ps[e]));
+  __syncwarp();
+  if (lane == 0) lse[li] = ln;
+}
+
+}  // namespace
+
+void combine_fwd(const Params &p, cudaStream_t s) {
+  FA_CHECK(p.d % 4 == 0, "combine: head_size must be a multiple of 4");
+  const int64_t n_items = (int64_t)p.b * p.seqlen_q * p.h;
+  dim3 grid((unsigned)((n_items + 3) / 4));
+  if (p.is_bf16) combine_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(p);
+  else combine_kernel<__half><<<grid, 128, 0, s>>>(p);
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void flashmask_prepare(const Params &p, int block_n, cudaStream_t s) {
+  FA_CHECK(block_n > 0, "flashmask_prepare: block_n must be positive");
+  const int nblock = ceil_div(p.seqlen_k, block_n);
+  const int nblock_pad = (nblock + 3) & ~3;
+  dim3 grid(ceil_div(nblock_pad, 4), p.b * p.h_mask);
+  flashmask_scan_kernel<<<grid, 128, 0, s>>>(p, block_n, nblock, nblock_pad);
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,
+               int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16, int64_t nbs, int64_t nrs,
+               int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s) {
+  (void)is_bf16;
+  FA_CHECK(nbs % 8 == 0 && nrs % 8 == 0 && nhs % 8 == 0 && cbs % 8 == 0 && crs % 8 == 0 && chs % 8 == 0,
+           "append_kv: strides must be multiples of 8 elements");
+  FA_CHECK(((uintptr_t)k_new | (uintptr_t)v_new | (uintptr_t)k_cache | (uintptr_t)v_cache) % 16 == 0,
+           "append_kv: tensors must be 16-byte aligned");
+  const int64_t total = (int64_t)batch * seqlen_new * h_k * (d / 8);
+  int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+  if (blocks < 1) blocks = 1;
+  append_kv_kernel<<<blocks, 256, 0, s>>>((const uint4 *)k_new, (const uint4 *)v_new, (uint4 *)k_cache, (uint4 *)v_cache,
+                                         cache_seqlens, batch, seqlen_new, seqlen_cache, h_k, d / 8, nbs, nrs, nhs, cbs,
+                                         crs, chs);
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
+               int is_bf16, int o_is_fp32, int64_t lrs, int64_t lhs, cudaStream_t s) {
+  dim3 grid((unsigned)((rows * heads + 3) / 4));
+  if (o_is_fp32) {
+    if (is_bf16) lse_merge_kernel<float, __nv_bfloat16><<<grid, 128, 0, s>>>((float *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs);
+    else lse_merge_kernel<float, __half><<<grid, 128, 0, s>>>((float *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs);
+  } else {
+    if (is_bf16) lse_merge_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 128, 0, s>>>((__nv_bfloat16 *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs);
+    else lse_merge_kernel<__half, __half><<<grid, 128, 0, s>>>((__half *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs);
+  }
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+}  // namespace fa

@@ -1,0 +1,255 @@
+// capi.cu -- the flat FlashAttention-2 style symbols of include/fa_capi.h.
+//
+// Each function translates the reference's argument list (csrc/capi/flash_attn.h) into fa_b200_params
+// the way set_params_fprop_strided / set_params_dgrad_strided do (csrc/capi/flash_attn.cu:98-229,231-300),
+// then takes the same dispatcher as the descriptor entry points.  FA2-surface semantics are fixed here:
+// top-left causal alignment, +inf LSE for rows without a visible key, per-q-head (expanded) dK/dV.
+#include <cstring>
+
+#include "common.h"
+#include "../../include/fa_capi.h"
+
+namespace {
+
+using fa::Params;
+
+void unsupported(bool cond, const char *what) {
+  if (cond) throw fa::Error(std::string(what) + " is not supported by libflashattn_b200 (SURVEY.md 8(f))");
+}
+
+Params base_params(int batch_size, int seqlen_q, int seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded,
+                   int num_heads, int num_heads_k, int head_size, int head_size_rounded, float softmax_scale,
+                   bool is_causal, bool is_bf16) {
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.abi_version = FA_B200_ABI_VERSION;
+  p.is_bf16 = is_bf16 ? 1 : 0;
+  p.b = batch_size; p.seqlen_q = seqlen_q; p.seqlen_k = seqlen_k;
+  p.h = num_heads; p.h_k = num_heads_k; p.d = head_size;
+  p.seqlen_q_rounded = seqlen_q_rounded; p.seqlen_k_rounded = seqlen_k_rounded; p.d_rounded = head_size_rounded;
+  p.total_q = p.total_k = -1;
+  p.softmax_scale = softmax_scale;
+  p.is_causal = is_causal ? 1 : 0;
+  p.causal_bottom_right = 0;
+  p.window_left = p.window_right = -1;
+  p.lse_empty_is_neg_inf = 0;
+  return p;
+}
+
+fa_b200_tensor tensor(const void *ptr, int batch_stride, int row_stride, int head_stride) {
+  fa_b200_tensor t;
+  t.ptr = const_cast<void *>(ptr);
+  t.batch_stride = batch_stride; t.row_stride = row_stride; t.head_stride = head_stride;
+  return t;
+}
+
+void set_flashmask(Params &p, const void *downstart, const int64_t *dims, const void *upend, const void *downend,
+                   const void *upstart, const void *maxmin) {
+  if (!downstart && !upend && !downend && !upstart) return;
+  FA_CHECK(downstart != nullptr, "flashmask_downstart_ptr is mandatory when any flashmask vector is given");
+  FA_CHECK(dims != nullptr, "flashmask_dims must be given");
+  // dims = (batch, mask heads, seqlen_k): csrc/capi/flash_attn.cu:623
+  FA_CHECK(dims[0] == p.b, "flashmask_dims[0] must equal batch_size");
+  FA_CHECK(dims[2] == p.seqlen_k, "flashmask_dims[2] must equal seqlen_k");
+  // csrc/capi/flash_attn.cu:204-210: the workspace is required whenever a vector is given
+  FA_CHECK(maxmin != nullptr, "flashmask_maxmin_ptr workspace must be given with flashmask vectors");
+  p.h_mask = (int)dims[1];
+  p.lt_start = (const int32_t *)downstart;
+  p.lt_end = (const int32_t *)downend;
+  p.ut_start = (const int32_t *)upstart;
+  p.ut_end = (const int32_t *)upend;
+  p.flashmask_maxmin = (int32_t *)const_cast<void *>(maxmin);
+}
+
+}  // namespace
+
+#define FA_BEGIN try {
+#define FA_END                                                \
+  }                                                           \
+  catch (const std::exception &e) {                           \
+    flash_attn_set_error(e.what());                           \
+    return false;                                             \
+  }                                                           \
+  catch (...) {                                               \
+    flash_attn_set_error(nullptr);                            \
+    return false;                                             \
+  }                                                           \
+  return true;
+
+extern "C" {
+
+bool flash_attn_fwd(
+    const void *q, const void *k, const void *v, void *rng_state, void *out, void *softmax_ptr,
+    void *softmax_lse_ptr, int batch_size, int seqlen_q, int seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded,
+    int num_heads, int num_heads_k, int head_size, int head_size_rounded, float p_dropout, float softmax_scale,
+    float softmax_unscale, bool is_causal, bool return_softmax, bool is_bf16, cudaStream_t stream, uint64_t seed,
+    uint64_t offset, const void *attn_mask, const int64_t *mask_dims, const void *flashmask_downstart_ptr,
+    const int64_t *flashmask_dims, const void *flashmask_upend_ptr, const void *flashmask_downend_ptr,
+    const void *flashmask_upstart_ptr, const void *flashmask_maxmin_ptr, int q_row_stride, int k_row_stride,
+    int v_row_stride, int q_head_stride, int k_head_stride, int v_head_stride, int o_row_stride, int o_head_stride,
+    int q_batch_stride, int k_batch_stride, int v_batch_stride, int o_batch_stride) {
+  FA_BEGIN
+  unsupported(p_dropout > 0.f, "dropout");
+  unsupported(return_softmax, "return_softmax");
+  unsupported(attn_mask != nullptr, "dense attn_mask");
+  Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
+                         head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
+  p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
+  p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
+  p.o = tensor(out, o_batch_stride, o_row_stride, o_head_stride);
+  p.softmax_lse = (float *)softmax_lse_ptr;
+  set_flashmask(p, flashmask_downstart_ptr, flashmask_dims, flashmask_upend_ptr, flashmask_downend_ptr,
+                flashmask_upstart_ptr, flashmask_maxmin_ptr);
+  if (rng_state) {  // the reference records (seed, offset) for backward replay (flash_attn.cu:672-677)
+    uint64_t st[2] = {seed, offset};
+    FA_CUDA(cudaMemcpyAsync(rng_state, st, sizeof(st), cudaMemcpyHostToDevice, stream));
+  }
+  (void)softmax_ptr; (void)softmax_unscale; (void)mask_dims;
+  fa::run_fwd(p, stream);
+  FA_END
+}
+
+bool flash_attn_varlen_fwd(
+    const void *q, const void *k, const void *v, const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k,
+    void *rng_state, void *out, void *softmax_ptr, void *softmax_lse_ptr, int batch_size, int max_seqlen_q,
+    int max_seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size,
+    int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale, bool is_causal,
+    bool return_softmax, bool is_bf16, cudaStream_t stream, uint64_t seed, uint64_t offset, const void *attn_mask,
+    const void *mask_dims, int q_row_stride, int k_row_stride, int v_row_stride, int q_head_stride, int k_head_stride,
+    int v_head_stride, int o_row_stride, int o_head_stride, int q_batch_stride, int k_batch_stride, int v_batch_stride,
+    int o_batch_stride, bool varlen_padded_input) {
+  FA_BEGIN
+  unsupported(p_dropout > 0.f, "dropout");
+  unsupported(return_softmax, "return_softmax");
+  unsupported(attn_mask != nullptr, "dense attn_mask");
+  FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
+  Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
+                         num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
+  p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
+  p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
+  p.o = tensor(out, o_batch_stride, o_row_stride, o_head_stride);
+  p.softmax_lse = (float *)softmax_lse_ptr;
+  p.cu_seqlens_q = cu_seqlens_q; p.cu_seqlens_k = cu_seqlens_k;
+  p.varlen_padded_input = varlen_padded_input ? 1 : 0;
+  if (rng_state) {
+    uint64_t st[2] = {seed, offset};
+    FA_CUDA(cudaMemcpyAsync(rng_state, st, sizeof(st), cudaMemcpyHostToDevice, stream));
+  }
+  (void)softmax_ptr; (void)softmax_unscale; (void)mask_dims;
+  fa::run_fwd(p, stream);
+  FA_END
+}
+
+bool flash_attn_bwd(
+    const void *dout, const void *q, const void *k, const void *v, const void *out, const void *softmax_d,
+    const void *softmax_lse, void *rng_state, void *dq, void *dk, void *dv, void *dq_accum, int batch_size,
+    int seqlen_q, int seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k,
+    int head_size, int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale, bool is_causal,
+    bool is_bf16, int num_splits, cudaStream_t stream, uint64_t seed, uint64_t offset, const void *attn_mask,
+    const int64_t *mask_dims, const void *flashmask_downstart_ptr, const int64_t *flashmask_dims,
+    const void *flashmask_upend_ptr, const void *flashmask_downend_ptr, const void *flashmask_upstart_ptr,
+    const void *flashmask_maxmin_ptr, int q_row_stride, int k_row_stride, int v_row_stride, int q_head_stride,
+    int k_head_stride, int v_head_stride, int o_row_stride, int o_head_stride, int q_batch_stride, int k_batch_stride,
+    int v_batch_stride, int o_batch_stride, int dq_row_stride, int dk_row_stride, int dv_row_stride,
+    int dq_head_stride, int dk_head_stride, int dv_head_stride, int do_row_stride, int do_head_stride,
+    int dq_batch_stride, int dk_batch_stride, int dv_batch_stride, int do_batch_stride) {
+  FA_BEGIN
+  unsupported(p_dropout > 0.f, "dropout");
+  unsupported(attn_mask != nullptr, "dense attn_mask");
+  Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
+                         head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
+  p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
+  p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
+  p.o = tensor(out, o_batch_stride, o_row_stride, o_head_stride);
+  p.dout = tensor(dout, do_batch_stride, do_row_stride, do_head_stride);
+  p.dq = tensor(dq, dq_batch_stride, dq_row_stride, dq_head_stride);
+  p.dk = tensor(dk, dk_batch_stride, dk_row_stride, dk_head_stride);
+  p.dv = tensor(dv, dv_batch_stride, dv_row_stride, dv_head_stride);
+  p.softmax_lse = (float *)const_cast<void *>(softmax_lse);
+  p.softmax_d = (float *)const_cast<void *>(softmax_d);
+  p.dq_accum = (float *)dq_accum;
+  p.dkv_expanded = 1;                       // csrc/flash_attn/src/flash_bwd_kernel.h:1077-1080
+  p.deterministic = (num_splits == 1);      // csrc/flash_attn/src/flash_bwd_kernel.h:3203-3208
+  set_flashmask(p, flashmask_downstart_ptr, flashmask_dims, flashmask_upend_ptr, flashmask_downend_ptr,
+                flashmask_upstart_ptr, flashmask_maxmin_ptr);
+  (void)rng_state; (void)seed; (void)offset; (void)softmax_unscale; (void)mask_dims;
+  fa::run_bwd(p, stream);
+  FA_END
+}
+
+bool flash_attn_varlen_bwd(
+    const void *dout, const void *q, const void *k, const void *v, const void *out, const void *softmax_d,
+    const void *softmax_lse, const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, void *rng_state, void *dq,
+    void *dk, void *dv, void *dq_accum, int batch_size, int max_seqlen_q, int max_seqlen_k, int seqlen_q_rounded,
+    int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size, int head_size_rounded, float p_dropout,
+    float softmax_scale, float softmax_unscale, bool is_causal, bool is_bf16, int num_splits, cudaStream_t stream,
+    uint64_t seed, uint64_t offset, const void *attn_mask, const int64_t *mask_dims, int q_row_stride,
+    int k_row_stride, int v_row_stride, int q_head_stride, int k_head_stride, int v_head_stride, int o_row_stride,
+    int o_head_stride, int q_batch_stride, int k_batch_stride, int v_batch_stride, int o_batch_stride,
+    int dq_row_stride, int dk_row_stride, int dv_row_stride, int dq_head_stride, int dk_head_stride,
+    int dv_head_stride, int do_row_stride, int do_head_stride, int dq_batch_stride, int dk_batch_stride,
+    int dv_batch_stride, int do_batch_stride, bool varlen_padded_input) {
+  FA_BEGIN
+  unsupported(p_dropout > 0.f, "dropout");
+  unsupported(attn_mask != nullptr, "dense attn_mask");
+  FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
+  Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
+                         num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
+  p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
+  p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
+  p.o = tensor(out, o_batch_stride, o_row_stride, o_head_stride);
+  p.dout = tensor(dout, do_batch_stride, do_row_stride, do_head_stride);
+  p.dq = tensor(dq, dq_batch_stride, dq_row_stride, dq_head_stride);
+  p.dk = tensor(dk, dk_batch_stride, dk_row_stride, dk_head_stride);
+  p.dv = tensor(dv, dv_batch_stride, dv_row_stride, dv_head_stride);
+  p.softmax_lse = (float *)const_cast<void *>(softmax_lse);
+  p.softmax_d = (float *)const_cast<void *>(softmax_d);
+  p.dq_accum = (float *)dq_accum;
+  p.cu_seqlens_q = cu_seqlens_q; p.cu_seqlens_k = cu_seqlens_k;
+  p.varlen_padded_input = varlen_padded_input ? 1 : 0;
+  p.dkv_expanded = 1;
+  p.deterministic = (num_splits == 1);
+  (void)rng_state; (void)seed; (void)offset; (void)softmax_unscale; (void)mask_dims;
+  fa::run_bwd(p, stream);
+  FA_END
+}
+
+bool calc_reduced_attn_scores(
+    const void *q, const void *k, const void *softmax_lse, void *reduced_scores, void *softmax_ptr, int batch_size,
+    int seqlen_q, int seqlen_k, int num_heads, int num_heads_k, int head_size, float softmax_scale,
+    bool return_softmax, bool is_bf16, int num_splits, cudaStream_t stream, int q_row_stride, int k_row_stride,
+    int o_row_stride, int q_head_stride, int k_head_stride, int o_head_stride, int q_batch_stride,
+    int k_batch_stride, int o_batch_stride) {
+  FA_BEGIN
+  unsupported(return_softmax, "return_softmax");
+  FA_CHECK(q && k && softmax_lse && reduced_scores, "calc_reduced_attn_scores: null tensor");
+  FA_CHECK(head_size % 8 == 0 && head_size <= 256 && num_heads % num_heads_k == 0, "unsupported head configuration");
+  fa::reduced_scores(q, k, (const float *)softmax_lse, (float *)reduced_scores, batch_size, seqlen_q, seqlen_k,
+                     num_heads, num_heads_k, head_size, softmax_scale, is_bf16, q_batch_stride, q_row_stride,
+                     q_head_stride, k_batch_stride, k_row_stride, k_head_stride, stream);
+  (void)softmax_ptr; (void)num_splits; (void)o_row_stride; (void)o_head_stride; (void)o_batch_stride;
+  FA_END
+}
+
+bool flash_attn_fwd_with_bias_and_mask(
+    const void *, const void *, const void *, void *, const int32_t *, const int32_t *, int, int, int, int, int, int,
+    int, float, float, bool, bool, int, void *, void *, uint64_t *, cudaStream_t, uint64_t, uint64_t, const void *,
+    const void *, const int64_t *, const int64_t *) {
+  flash_attn_set_error("flash_attn_fwd_with_bias_and_mask (legacy FA1 bias+mask path) is not supported by libflashattn_b200");
+  return false;
+}
+
+bool flash_attn_bwd_with_bias_and_mask(
+    const void *, const void *, const void *, void *, void *, void *, const void *, const void *, const int32_t *,
+    const int32_t *, int, int, int, int, int, int, int, float, float, bool, bool, int, const void *, void *, void *,
+    void *, uint64_t *, cudaStream_t, uint64_t, uint64_t, const void *, const void *, const int64_t *,
+    const int64_t *) {
+  flash_attn_set_error("flash_attn_bwd_with_bias_and_mask (legacy FA1 bias+mask path) is not supported by libflashattn_b200");
+  return false;
+}
+
+}  // extern "C"

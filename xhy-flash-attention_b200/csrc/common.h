@@ -36,16 +36,26 @@ void note_launch(int kind);  // kind: 1 generic SIMT, 2 tcgen05
 int device_sm_count();
 int device_cc_major();
 
+// dispatchers (api.cu)
+void run_fwd(const Params &p, cudaStream_t s);
+void run_bwd(const Params &p, cudaStream_t s);
+void run_splitkv(const Params &p, cudaStream_t s);
+
 // ---- kernel families -------------------------------------------------------------------------
 // generic SIMT kernels: any head_size % 8 == 0 up to 256, every mask kind, both dtypes.
 void generic_fwd(const Params &p, cudaStream_t s);
 void generic_bwd(const Params &p, cudaStream_t s);
+void generic_splitkv_fwd(const Params &p, cudaStream_t s);
+void reduced_scores(const void *q, const void *k, const float *lse, float *out, int b, int sq, int sk, int h, int h_k,
+                    int d, float scale, int is_bf16, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs, int64_t krs,
+                    int64_t khs, cudaStream_t s);
 // tcgen05 / TMA / TMEM kernels (sm_100a): return false when the shape is outside their envelope.
 bool sm100_fwd_supported(const Params &p, std::string *why);
 void sm100_fwd(const Params &p, cudaStream_t s);
 bool sm100_bwd_supported(const Params &p, std::string *why);
 void sm100_bwd(const Params &p, cudaStream_t s);
 // bandwidth kernels
+void splitkv_fwd(const Params &p, cudaStream_t s);
 void combine_fwd(const Params &p, cudaStream_t s);
 void flashmask_prepare(const Params &p, int block_n, cudaStream_t s);
 void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,

@@ -1,0 +1,480 @@
+// sm100_fwd.cu -- the tcgen05 / TMEM / TMA forward kernel (sm_100a).
+//
+// Computes what the reference's compute_attn_1rowblock computes (csrc/flash_attn/src/flash_fwd_kernel.h:121-583:
+// O = softmax(scale * Q K^T + mask) V and LSE), restructured for Blackwell:
+//
+//   * persistent CTAs, one per SM; a work tile is 256 query rows (two 128-row Q tiles) of one (batch, q-head);
+//   * warp 9  : TMA producer -- Q tiles once per work tile, K/V tiles through a 4-stage shared-memory ring;
+//   * warp 8  : MMA issuer   -- S_t = Q_t K_j^T (tcgen05.mma, SS) into TMEM, O_t += P_t V_j (tcgen05.mma, TS: P read from TMEM);
+//   * warps 0-3 / 4-7 : softmax warpgroups for Q tile 0 / 1 -- one thread per query row (TMEM lane == row, so row max
+//     and row sum need no shuffles), exp2 with the folded scale, lazy (thresholded) O rescale, P written back over S in
+//     TMEM as packed 16-bit, epilogue O -> smem -> coalesced global stores, LSE.
+//   The two Q tiles ping-pong on the tensor core: while one warpgroup runs softmax the MMA warp works for the other.
+//
+// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,256+HD) O1 [256+HD, 256+2HD).
+#include <math_constants.h>
+#include <type_traits>
+
+#include "common.h"
+#include "sm100.cuh"
+
+namespace fa {
+namespace {
+
+using namespace sm100;
+
+constexpr int kBM = 128;          // rows per Q tile
+constexpr int kBN = 128;          // keys per K/V tile
+constexpr int kTilesPerCta = 2;   // Q tiles per work tile
+constexpr int kStages = 4;        // K/V ring depth
+constexpr int kThreads = 320;     // 2 softmax warpgroups + MMA warp + TMA warp
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kRescaleThreshold = 8.0f;  // log2 domain: P stays below 2^8
+
+struct FwdTma {
+  CUtensorMap q, k, v;
+};
+
+template <int HD> struct FwdSmem {
+  static constexpr int kTileBytes = kBM * HD * 2;               // one Q or K or V tile
+  static constexpr int kQOff = 0;
+  static constexpr int kKVOff = kTilesPerCta * kTileBytes;
+  static constexpr int kBarOff = kKVOff + kStages * kTileBytes;
+  static constexpr int kNumBars = 2 + 2 + kStages * 2 + 2 + 2 + 2;
+  static constexpr int kTmemSlotOff = kBarOff + kNumBars * 8;
+  static constexpr int kTotal = kTmemSlotOff + 16;
+  static constexpr int kDynBytes = kTotal + 1024;               // slack for manual 1024-byte alignment
+};
+
+struct TileInfo {
+  int bi, hq, hk, m0;
+  int sq, sk, q_row0, k_row0, q_b, k_b;
+  bool active[2];
+  int n_lo[2], n_hi[2];
+  int lo, hi;  // union block range
+};
+
+__device__ __forceinline__ bool decode_tile(const Params &p, int tile, int num_m, TileInfo &ti) {
+  const int g = p.h / p.h_k;
+  const int per_seg = g * num_m;
+  const int seg = tile / per_seg, pos = tile % per_seg;
+  ti.bi = seg / p.h_k;
+  ti.hk = seg % p.h_k;
+  ti.hq = ti.hk * g + pos % g;
+  ti.m0 = (num_m - 1 - pos / g) * (kBM * kTilesPerCta);
+  bool qb, kb;
+  seq_bounds(p, ti.bi, ti.q_row0, ti.sq, ti.k_row0, ti.sk, qb, kb);
+  ti.q_b = qb ? ti.bi : 0;
+  ti.k_b = kb ? ti.bi : 0;
+  if (ti.m0 >= ti.sq) return false;
+  const int shift = ti.sk - ti.sq;
+  const int shiftc = p.causal_bottom_right ? shift : 0;
+  ti.lo = 0x7fffffff; ti.hi = 0;
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int r0 = ti.m0 + t * kBM;
+    ti.active[t] = r0 < ti.sq;
+    const int r1 = min(r0 + kBM, ti.sq);
+    int hi_col = ti.sk, lo_col = 0;
+    if (p.is_causal) hi_col = min(hi_col, r1 - 1 + shiftc + 1);
+    if (p.window_right >= 0) hi_col = min(hi_col, r1 - 1 + shift + p.window_right + 1);
+    if (p.window_left >= 0) lo_col = max(lo_col, r0 + shift - p.window_left);
+    int nlo = lo_col / kBN, nhi = (max(hi_col, 0) + kBN - 1) / kBN;
+    if (!ti.active[t] || nhi <= nlo) { nlo = 0; nhi = 0; }
+    ti.n_lo[t] = nlo; ti.n_hi[t] = nhi;
+    if (nhi > nlo) { ti.lo = min(ti.lo, nlo); ti.hi = max(ti.hi, nhi); }
+  }
+  if (ti.hi == 0) ti.lo = 0;
+  return true;
+}
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int HD, bool kBf16>
+__global__ void __launch_bounds__(kThreads, 1)
+fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles) {
+  using L = FwdSmem<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  // barrier addresses
+  auto bar = [&](int i) { return sbase + L::kBarOff + i * 8; };
+  const int B_QFULL = 0, B_QEMPTY = 2, B_KVFULL = 4, B_KVEMPTY = 4 + kStages, B_SFULL = 4 + 2 * kStages,
+            B_PFULL = B_SFULL + 2, B_OFULL = B_PFULL + 2;
+  uint32_t *tmem_slot = (uint32_t *)(smem + L::kTmemSlotOff);
+
+  if (threadIdx.x == 0) {
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(bar(B_QFULL + t), 1);
+      mbar_init(bar(B_QEMPTY + t), kBM);
+      mbar_init(bar(B_SFULL + t), 1);
+      mbar_init(bar(B_PFULL + t), kBM);
+      mbar_init(bar(B_OFULL + t), 1);
+    }
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar(B_KVFULL + s), 1);
+      mbar_init(bar(B_KVEMPTY + s), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc<512>(smem_u32(tmem_slot));
+  if (warp == 9 && lane == 0) {
+    tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  constexpr int kHalves = HD / 64;            // 64-element (128-byte) boxes per row
+  constexpr uint32_t kHalfBytes = kBM * 128;  // one box: 128 rows x 128 bytes
+  const uint32_t scale_dummy = 0; (void)scale_dummy;
+
+  if (warp == 9) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      uint32_t kv_it = 0, qcnt[2] = {0, 0};
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        TileInfo ti;
+        if (!decode_tile(p, tile, num_m, ti)) continue;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          if (ti.n_hi[t] <= ti.n_lo[t]) continue;
+          mbar_wait(bar(B_QEMPTY + t), (qcnt[t] & 1) ^ 1);
+          mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
+#pragma unroll
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + hf * kHalfBytes, &tm.q, bar(B_QFULL + t), hf * 64, ti.hq,
+                        ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
+          ++qcnt[t];
+        }
+        for (int j = ti.lo; j < ti.hi; ++j) {
+#pragma unroll
+          for (int kv = 0; kv < 2; ++kv) {
+            const uint32_t st = kv_it % kStages, ph = (kv_it / kStages) & 1;
+            mbar_wait(bar(B_KVEMPTY + st), ph ^ 1);
+            mbar_expect_tx(bar(B_KVFULL + st), L::kTileBytes);
+#pragma unroll
+            for (int hf = 0; hf < kHalves; ++hf)
+              tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + hf * kHalfBytes, kv == 0 ? &tm.k : &tm.v,
+                          bar(B_KVFULL + st), hf * 64, ti.hk, ti.k_row0 + j * kBN, ti.k_b);
+            ++kv_it;
+          }
+        }
+      }
+    }
+  } else if (warp == 8) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc(kBf16, kBM, kBN, false, false);
+      constexpr uint32_t idesc_o = make_idesc(kBf16, kBM, HD, false, true);
+      uint32_t kv_it = 0, qcnt[2] = {0, 0}, pcnt[2] = {0, 0};
+      auto issue_s = [&](int t, uint32_t kstage) {
+        const uint32_t qa = sbase + L::kQOff + t * L::kTileBytes;
+        const uint32_t ka = sbase + L::kKVOff + kstage * L::kTileBytes;
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) {
+          const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
+          umma_ss(tmem + t * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
+                  k > 0);
+        }
+        umma_commit(bar(B_SFULL + t));
+      };
+      auto issue_pv = [&](int t, uint32_t vstage, bool accumulate) {
+        const uint32_t va = sbase + L::kKVOff + vstage * L::kTileBytes;
+#pragma unroll
+        for (int k = 0; k < kBN / 16; ++k)
+          umma_ts(tmem + 2 * kBN + t * HD, tmem + t * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kHalfBytes, 1024),
+                  idesc_o, (accumulate || k > 0) ? 1u : 0u);
+        umma_commit(bar(B_OFULL + t));
+      };
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        TileInfo ti;
+        if (!decode_tile(p, tile, num_m, ti)) continue;
+        if (ti.hi <= ti.lo) continue;
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+          if (ti.n_hi[t] > ti.n_lo[t]) { mbar_wait(bar(B_QFULL + t), qcnt[t] & 1); ++qcnt[t]; }
+        // first K tile
+        uint32_t kst = kv_it % kStages;
+        mbar_wait(bar(B_KVFULL + kst), (kv_it / kStages) & 1);
+        ++kv_it;
+        tc_fence_after();
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+          if (ti.lo >= ti.n_lo[t] && ti.lo < ti.n_hi[t]) issue_s(t, kst);
+        umma_commit(bar(B_KVEMPTY + kst));
+        for (int j = ti.lo; j < ti.hi; ++j) {
+          const uint32_t vst = kv_it % kStages;
+          mbar_wait(bar(B_KVFULL + vst), (kv_it / kStages) & 1);
+          ++kv_it;
+          const bool has_next = j + 1 < ti.hi;
+          uint32_t nkst = 0;
+          bool next_waited = false;
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            if (j >= ti.n_lo[t] && j < ti.n_hi[t]) {
+              mbar_wait(bar(B_PFULL + t), pcnt[t] & 1);
+              ++pcnt[t];
+              tc_fence_after();
+              issue_pv(t, vst, j > ti.n_lo[t]);
+            }
+            if (has_next && j + 1 >= ti.n_lo[t] && j + 1 < ti.n_hi[t]) {
+              if (!next_waited) {
+                nkst = kv_it % kStages;
+                mbar_wait(bar(B_KVFULL + nkst), (kv_it / kStages) & 1);
+                tc_fence_after();
+                next_waited = true;
+              }
+              issue_s(t, nkst);
+            }
+          }
+          umma_commit(bar(B_KVEMPTY + vst));
+          if (has_next) {
+            if (!next_waited) {  // no tile uses block j+1 (cannot happen for the union range, kept for safety)
+              nkst = kv_it % kStages;
+              mbar_wait(bar(B_KVFULL + nkst), (kv_it / kStages) & 1);
+            }
+            ++kv_it;
+            umma_commit(bar(B_KVEMPTY + nkst));
+          }
+        }
+      }
+    }
+  } else {
+    // ======================= softmax warpgroups =======================
+    const int t = warp / 4;                    // Q tile of this warpgroup
+    const int r_in_tile = threadIdx.x - t * kBM;
+    const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
+    const uint32_t tS = tmem + lane_base + t * kBN;
+    const uint32_t tO = tmem + lane_base + 2 * kBN + t * HD;
+    const float scale_log2 = p.softmax_scale * kLog2e;
+    uint32_t scnt = 0, ocnt = 0;
+    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileInfo ti;
+      if (!decode_tile(p, tile, num_m, ti)) continue;
+      if (!ti.active[t]) continue;
+      const int row = ti.m0 + t * kBM + r_in_tile;
+      const int nlo = ti.n_lo[t], nhi = ti.n_hi[t];
+      T *optr = (T *)p.o.ptr + (int64_t)ti.q_b * p.o.batch_stride + (int64_t)(ti.q_row0) * p.o.row_stride +
+                (int64_t)ti.hq * p.o.head_stride;
+      float *lse_ptr = p.softmax_lse + ((int64_t)ti.bi * p.h + ti.hq) * p.seqlen_q;
+      if (nhi <= nlo) {
+        // no visible key block for this Q tile: out = 0, lse = +-inf
+        if (row < ti.sq) {
+          T *orow = optr + (int64_t)row * p.o.row_stride;
+          for (int e = 0; e < p.d; e += 8) *reinterpret_cast<uint4 *>(orow + e) = make_uint4(0, 0, 0, 0);
+          lse_ptr[row] = p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F;
+        }
+        continue;
+      }
+      const MaskCtx mc = make_mask_ctx(p, ti.bi, ti.hq, ti.sq, ti.sk);
+      const int shiftc = mc.bottom_right ? mc.shift : 0;
+      const int r0 = ti.m0 + t * kBM;
+      float m_ref = -CUDART_INF_F, l = 0.f;
+      for (int j = nlo; j < nhi; ++j) {
+        mbar_wait(bar(B_SFULL + t), scnt & 1);
+        ++scnt;
+        tc_fence_after();
+        uint32_t s[4][32];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+        tmem_wait_ld();
+        const int c0 = j * kBN;
+        const bool full = (c0 + kBN <= ti.sk) && (!mc.causal || c0 + kBN - 1 <= r0 + shiftc) &&
+                          (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
+                          (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) && (mc.lts == nullptr);
+        if (!full) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (is_masked(mc, row, c0 + c * 32 + i)) s[c][i] = __float_as_uint(-CUDART_INF_F);
+        }
+        float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[0][i]));
+          mx1 = fmaxf(mx1, __uint_as_float(s[1][i]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[2][i]));
+          mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+        if (j == nlo) {
+          m_ref = mx;
+        } else {
+          const bool need = (mx > m_ref) && ((mx - m_ref) * scale_log2 > kRescaleThreshold || m_ref == -CUDART_INF_F);
+          if (__any_sync(0xffffffffu, need)) {
+            // the previous PV of this tile must have landed in O before it is rescaled
+            mbar_wait(bar(B_OFULL + t), (ocnt + (uint32_t)(j - nlo - 1)) & 1);
+            tc_fence_after();
+            const float m_new = fmaxf(m_ref, mx);
+            const float corr = (m_new == -CUDART_INF_F) ? 1.f : ex2((m_ref - m_new) * scale_log2);
+            l *= corr;
+            m_ref = m_new;
+#pragma unroll
+            for (int c = 0; c < HD / 32; ++c) {
+              uint32_t o[32];
+              tmem_ld32(tO + c * 32, o);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+              tmem_st32(tO + c * 32, o);
+            }
+          }
+        }
+        const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
+        float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float p0 = ex2(fmaf(__uint_as_float(s[c][2 * i]), scale_log2, -msc));
+            const float p1 = ex2(fmaf(__uint_as_float(s[c][2 * i + 1]), scale_log2, -msc));
+            sum0 += p0; sum1 += p1;
+            pk[i] = pack2<kBf16>(p0, p1);
+          }
+          tmem_st16(tS + c * 16, pk);
+        }
+        l += sum0 + sum1;
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar(B_PFULL + t));
+      }
+      // ---------------- epilogue ----------------
+      mbar_wait(bar(B_OFULL + t), (ocnt + (uint32_t)(nhi - nlo - 1)) & 1);
+      ocnt += (uint32_t)(nhi - nlo);
+      tc_fence_after();
+      const float inv = (l > 0.f) ? 1.f / l : 0.f;
+      uint8_t *stage = smem + L::kQOff + t * L::kTileBytes;  // Q_t is dead: all S MMAs of this tile have completed
+      constexpr int kChunks = HD / 8;                        // 16-byte chunks per row
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(tO + c * 32, o);
+        tmem_wait_ld();
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 v;
+          v.x = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 0]) * inv, __uint_as_float(o[q4 * 8 + 1]) * inv);
+          v.y = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 2]) * inv, __uint_as_float(o[q4 * 8 + 3]) * inv);
+          v.z = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 4]) * inv, __uint_as_float(o[q4 * 8 + 5]) * inv);
+          v.w = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 6]) * inv, __uint_as_float(o[q4 * 8 + 7]) * inv);
+          const int chunk = c * 4 + q4;
+          *reinterpret_cast<uint4 *>(stage + r_in_tile * (HD * 2) + ((chunk ^ (r_in_tile & (kChunks - 1))) * 16)) = v;
+        }
+      }
+      tc_fence_before();
+      if (row < ti.sq)
+        lse_ptr[row] = (l > 0.f) ? (m_ref * p.softmax_scale + __logf(l))
+                                 : (p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F);
+      named_bar_sync(1 + t, kBM);
+      {
+        const int chunk = r_in_tile % kChunks;
+        const int rsub = r_in_tile / kChunks;
+        constexpr int kRowsPerPass = kBM / kChunks;
+#pragma unroll 4
+        for (int pass = 0; pass < kBM / kRowsPerPass; ++pass) {
+          const int rr = pass * kRowsPerPass + rsub;
+          const int grow = ti.m0 + t * kBM + rr;
+          if (grow < ti.sq && chunk * 8 < p.d) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(stage + rr * (HD * 2) + ((chunk ^ (rr & (kChunks - 1))) * 16));
+            *reinterpret_cast<uint4 *>(optr + (int64_t)grow * p.o.row_stride + chunk * 8) = v;
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(bar(B_QEMPTY + t));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc<512>(tmem);
+}
+
+void sanitize(TmaDesc4 &d) {
+  // a dimension of extent 1 never advances: give it any legal (16-byte multiple) stride
+  for (int i = 1; i < 4; ++i)
+    if (d.dims[i] == 1) d.strides[i - 1] = 16;
+}
+
+TmaDesc4 desc_for(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch, int box_rows) {
+  TmaDesc4 x;
+  x.ptr = t.ptr;
+  x.dims[0] = (uint64_t)d; x.dims[1] = (uint64_t)heads; x.dims[2] = (uint64_t)rows; x.dims[3] = (uint64_t)batch;
+  x.strides[0] = (uint64_t)t.head_stride * 2; x.strides[1] = (uint64_t)t.row_stride * 2;
+  x.strides[2] = (uint64_t)t.batch_stride * 2;
+  x.box[0] = 64; x.box[1] = 1; x.box[2] = (uint32_t)box_rows; x.box[3] = 1;
+  sanitize(x);
+  return x;
+}
+
+bool tma_ok(const fa_b200_tensor &t, int heads, int batch) {
+  if (((uintptr_t)t.ptr & 15) != 0) return false;
+  if (t.row_stride % 8 != 0 || t.row_stride <= 0) return false;
+  if (heads > 1 && (t.head_stride % 8 != 0 || t.head_stride <= 0)) return false;
+  if (batch > 1 && (t.batch_stride % 8 != 0 || t.batch_stride <= 0)) return false;
+  return true;
+}
+
+template <int HD, bool kBf16> void launch_fwd(const Params &p, cudaStream_t s) {
+  using L = FwdSmem<HD>;
+  const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
+  const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
+  FA_CHECK(!packed_q || p.total_q >= 0, "varlen: total_q must be given");
+  FA_CHECK(!packed_k || p.total_k >= 0, "varlen: total_k must be given");
+  FwdTma tm;
+  tm.q = make_tma_4d(desc_for(p.q, p.d, p.h, packed_q ? p.total_q : p.seqlen_q, packed_q ? 1 : p.b, kBM));
+  tm.k = make_tma_4d(desc_for(p.k, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
+  tm.v = make_tma_4d(desc_for(p.v, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
+  const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
+  const int num_tiles = p.b * p.h * num_m;
+  auto kern = fwd_kernel<HD, kBf16>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
+    attr_set = true;
+  }
+  const int grid = std::min(num_tiles, device_sm_count());
+  kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles);
+  FA_CUDA(cudaGetLastError());
+  note_launch(2);
+}
+
+}  // namespace
+
+bool sm100_fwd_supported(const Params &p, std::string *why) {
+  auto no = [&](const char *w) { if (why) *why = w; return false; };
+  if (p.d > 128) return no("head_size > 128");
+  if (p.num_splits > 1) return no("split-KV");
+  const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
+  if (p.cu_seqlens_q && !p.cu_seqlens_k) return no("cu_seqlens_q without cu_seqlens_k");
+  if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
+  if (p.cu_seqlens_k && !p.cu_seqlens_q) return no("cu_seqlens_k without cu_seqlens_q");
+  if (!tma_ok(p.q, p.h, packed ? 1 : p.b) || !tma_ok(p.k, p.h_k, packed ? 1 : p.b) ||
+      !tma_ok(p.v, p.h_k, packed ? 1 : p.b))
+    return no("strides/alignment not TMA-compatible");
+  if (((uintptr_t)p.o.ptr & 15) != 0 || p.o.row_stride % 8 != 0 || p.o.head_stride % 8 != 0 || p.o.batch_stride % 8 != 0)
+    return no("output not 16-byte aligned");
+  return true;
+}
+
+void sm100_fwd(const Params &p, cudaStream_t s) {
+  if (p.d <= 64) {
+    if (p.is_bf16) launch_fwd<64, true>(p, s); else launch_fwd<64, false>(p, s);
+  } else {
+    if (p.is_bf16) launch_fwd<128, true>(p, s); else launch_fwd<128, false>(p, s);
+  }
+}
+
+}  // namespace fa

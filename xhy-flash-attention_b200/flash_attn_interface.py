@@ -1,0 +1,507 @@
+"""Operator API -- drop-in for the reference's ``flash_attn/flash_attn_interface.py``.
+
+Same public names, positional order and defaults as the reference (flash_attn/__init__.py:3-8;
+flash_attn_interface.py:282-492), each backed by a ``torch.autograd.Function`` with the same
+save/return behaviour (:88-279).  The functions below differ from the reference only in what sits
+underneath: instead of the ``flash_attn_2_cuda`` pybind module they call the C ABI of
+``libflashattn_b200.so`` (``fa_b200_fwd`` / ``fa_b200_bwd``) through ctypes.
+
+Behaviour kept from the reference:
+  * ``softmax_scale=None`` -> ``headdim ** -0.5``                               (:220-221)
+  * non-unit last stride -> ``.contiguous()``; other strides are passed through  (:40-41)
+  * head dim not a multiple of 8 is zero-padded and sliced back                 (csrc/flash_attn/flash_api.cpp:238-247,318-321)
+  * ``return_attn_probs=True`` returns ``(out, softmax_lse, S_dmask)``; ``S_dmask`` is ``None``
+    unless dropout is active                                                    (:224,230)
+  * causal masks are TOP-LEFT aligned                                            (tests/test_flash_attn.py:144-146)
+  * packed inputs get one packed gradient tensor                                (:108-113,167-176)
+
+Dropout (``dropout_p > 0``) is not implemented in this build and raises.
+
+Added on top of the reference surface (keyword-only, all default to the reference behaviour):
+``window_size``, ``flashmask`` (the fork's column-sparse mask vectors), ``flash_attn_with_kvcache``
+(upstream signature; the fork has the capability only at C level, csrc/flash_attn_v3/flash.h:96-125) and
+``flashmask_attention``.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import _capi
+from ._capi import Params, new_params, ptr, round_up, tdesc
+
+
+def _maybe_contiguous(x):
+    return x.contiguous() if x is not None and x.stride(-1) != 1 else x
+
+
+def _pad_head(x, d_pad):
+    return x if x.shape[-1] == d_pad else F.pad(x, [0, d_pad - x.shape[-1]])
+
+
+class _Mask:
+    """Masking options beyond ``causal`` (all off by default)."""
+    __slots__ = ("window", "bottom_right", "lt_start", "lt_end", "ut_start", "ut_end", "lse_neg_inf", "force_generic")
+
+    def __init__(self, window=(-1, -1), bottom_right=False, flashmask=None, lse_neg_inf=False, force_generic=False):
+        self.window = tuple(window)
+        self.bottom_right = bottom_right or self.window != (-1, -1)
+        self.lt_start = self.lt_end = self.ut_start = self.ut_end = None
+        if flashmask is not None:
+            vecs = list(flashmask) + [None] * (4 - len(flashmask))
+            self.lt_start, self.lt_end, self.ut_start, self.ut_end = vecs[:4]
+            if self.lt_start is None:
+                raise ValueError("flashmask: lt_start is mandatory")
+        self.lse_neg_inf = lse_neg_inf
+        self.force_generic = force_generic
+
+
+_NO_MASK = _Mask()
+
+
+def _fill_mask(p: Params, mask: _Mask, b: int, sk: int, keep: list):
+    p.causal_bottom_right = 1 if mask.bottom_right else 0
+    p.window_left, p.window_right = mask.window
+    p.lse_empty_is_neg_inf = 1 if mask.lse_neg_inf else 0
+    p.force_generic = 1 if mask.force_generic else 0
+    if mask.lt_start is not None:
+        lts = mask.lt_start
+        assert lts.dtype == torch.int32 and lts.dim() == 3 and lts.shape[0] == b and lts.shape[2] == sk, \
+            "flashmask vectors must be int32 (batch, mask_heads, seqlen_k)"
+        p.h_mask = lts.shape[1]
+        for name in ("lt_start", "lt_end", "ut_start", "ut_end"):
+            t = getattr(mask, name)
+            if t is not None:
+                assert t.shape == lts.shape and t.dtype == torch.int32
+                t = t.contiguous()
+                keep.append(t)
+                setattr(p, name, t.data_ptr())
+        nblock = (((sk + 63) // 64) + 3) & ~3
+        ws = torch.empty(8 * b * p.h_mask * nblock, dtype=torch.int32, device=lts.device)
+        keep.append(ws)
+        p.flashmask_maxmin = ws.data_ptr()
+
+
+def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softmax, mask: _Mask = _NO_MASK,
+                        cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=None, max_seqlen_k=None,
+                        seqused_k=None):
+    """Equivalent of ``flash_attn_2_cuda.fwd`` / ``varlen_fwd`` (csrc/flash_attn/flash_api.cpp:186-324,326-491).
+
+    Returns ``(out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state)`` like the reference binding.
+    """
+    if dropout_p > 0.0:
+        raise NotImplementedError("dropout is not implemented in the B200 build (SURVEY.md 8(f))")
+    q, k, v = [_maybe_contiguous(x) for x in (q, k, v)]
+    if not q.is_cuda:
+        raise RuntimeError("q must be on CUDA device")  # flash_api.cpp:209
+    varlen = cu_seqlens_q is not None
+    d_og = q.shape[-1]
+    if d_og > 256:
+        raise RuntimeError("FlashAttention forward only supports head dimension at most 256")
+    if q.shape[-2] % k.shape[-2] != 0:
+        raise RuntimeError("Number of heads in key/value must divide number of heads in query")
+    d = round_up(d_og, 8)
+    q_p, k_p, v_p = [_pad_head(x, d) for x in (q, k, v)]
+    p = new_params(q.dtype)
+    keep = []
+    if varlen:
+        total_q, h, _ = q_p.shape
+        h_k = k_p.shape[1]
+        b = cu_seqlens_q.numel() - 1
+        sq, sk = int(max_seqlen_q), int(max_seqlen_k)
+        p.cu_seqlens_q, p.cu_seqlens_k = cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr()
+        p.total_q, p.total_k = total_q, k_p.shape[0]
+        out_p = torch.empty_like(q_p)
+    else:
+        b, sq, h, _ = q_p.shape
+        sk, h_k = k_p.shape[1], k_p.shape[2]
+        out_p = torch.empty_like(q_p)
+    if seqused_k is not None:
+        p.seqused_k = seqused_k.data_ptr()
+    lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
+    p.q, p.k, p.v, p.o = [tdesc(t, packed=varlen) for t in (q_p, k_p, v_p, out_p)]
+    p.softmax_lse = lse.data_ptr()
+    p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
+    p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+    p.softmax_scale = softmax_scale
+    p.is_causal = 1 if causal else 0
+    _fill_mask(p, mask, b, sk, keep)
+    with torch.cuda.device(q.device):
+        _capi.check(_capi.load().fa_b200_fwd(p, _capi.stream_ptr(q.device)), "fa_b200_fwd")
+    out = out_p[..., :d_og] if d != d_og else out_p
+    return out, q_p, k_p, v_p, out_p, lse, None, None
+
+
+def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p, softmax_scale, causal,
+                         rng_state=None, mask: _Mask = _NO_MASK, cu_seqlens_q=None, cu_seqlens_k=None,
+                         max_seqlen_q=None, max_seqlen_k=None, deterministic=False):
+    """Equivalent of ``flash_attn_2_cuda.bwd`` / ``varlen_bwd`` (csrc/flash_attn/flash_api.cpp:493-694,696-912).
+
+    ``q, k, v, out`` are the (head-padded) tensors saved by forward; ``dq, dk, dv`` are written in place
+    (they may be strided slices of a packed gradient).  GQA/MQA: dk/dv have ``h_k`` heads -- the group
+    reduction happens inside the kernels, not with an expanded buffer + ``sum`` as in the reference (:628-635,682-686).
+    """
+    dout, q, k, v, out = [_maybe_contiguous(x) for x in (dout, q, k, v, out)]
+    varlen = cu_seqlens_q is not None
+    d = q.shape[-1]
+    dout = _pad_head(dout, d)
+    p = new_params(q.dtype)
+    keep = []
+    if varlen:
+        total_q, h, _ = q.shape
+        h_k = k.shape[1]
+        b = cu_seqlens_q.numel() - 1
+        sq, sk = int(max_seqlen_q), int(max_seqlen_k)
+        p.cu_seqlens_q, p.cu_seqlens_k = cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr()
+        p.total_q, p.total_k = total_q, k.shape[0]
+    else:
+        b, sq, h, _ = q.shape
+        sk, h_k = k.shape[1], k.shape[2]
+    sq_r, sk_r, d_r = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+    softmax_d = torch.empty((b, h, sq_r), dtype=torch.float32, device=q.device)
+    # fp32 dQ accumulator: batch mode (b, h, sq_r, d_r); varlen mode h * (total_q + 128 * b) rows (one tile of
+    # slack per sequence so tile-granular reduce-adds never cross sequences)
+    acc_rows = (total_q + 128 * b) * h if varlen else b * h * sq_r
+    dq_accum = torch.empty(round_up(acc_rows, 128) * d_r, dtype=torch.float32, device=q.device)
+    p.q, p.k, p.v, p.o, p.dout, p.dq, p.dk, p.dv = [tdesc(t, packed=varlen) for t in (q, k, v, out, dout, dq, dk, dv)]
+    p.softmax_lse, p.softmax_d, p.dq_accum = softmax_lse.data_ptr(), softmax_d.data_ptr(), dq_accum.data_ptr()
+    if h != h_k:
+        rows_k = (p.total_k + 128 * b) if varlen else b * sk_r
+        dkv_accum = torch.empty(2 * h_k * rows_k * d_r, dtype=torch.float32, device=q.device)
+        keep.append(dkv_accum)
+        p.dkv_accum = dkv_accum.data_ptr()
+    p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
+    p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = sq_r, sk_r, d_r
+    p.softmax_scale = softmax_scale
+    p.is_causal = 1 if causal else 0
+    p.deterministic = 1 if deterministic else 0
+    _fill_mask(p, mask, b, sk, keep)
+    with torch.cuda.device(q.device):
+        _capi.check(_capi.load().fa_b200_bwd(p, _capi.stream_ptr(q.device)), "fa_b200_bwd")
+    return dq, dk, dv, softmax_d
+
+
+def _flash_attn_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
+                               softmax_scale, causal, return_softmax, mask: _Mask = _NO_MASK):
+    return _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softmax, mask,
+                               cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k)
+
+
+def _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
+                                max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale, causal, rng_state=None,
+                                mask: _Mask = _NO_MASK):
+    return _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p, softmax_scale, causal,
+                                rng_state, mask, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k)
+
+
+# ----------------------------------------------------------------------------------------------------
+# autograd Functions -- same six classes as the reference (flash_attn_interface.py:88-279)
+# ----------------------------------------------------------------------------------------------------
+class FlashAttnQKVPackedFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, dropout_p, softmax_scale, causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = qkv.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
+            qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], dropout_p, softmax_scale, causal=causal,
+            return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
+        ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse = ctx.saved_tensors
+        qkv_shape = q.shape[:-2] + (3, *q.shape[-2:])
+        dqkv = torch.empty(qkv_shape, dtype=q.dtype, device=q.device)
+        _flash_attn_backward(dout, q, k, v, out, softmax_lse, dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2],
+                             ctx.dropout_p, ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+        dqkv = dqkv[..., :dout.shape[-1]]  # the head dimension may have been padded
+        return dqkv, None, None, None, None, None
+
+
+class FlashAttnVarlenQKVPackedFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = qkv.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
+            qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens, max_seqlen, max_seqlen, dropout_p,
+            softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens)
+        ctx.dropout_p, ctx.max_seqlen, ctx.softmax_scale, ctx.causal, ctx.mask = \
+            dropout_p, max_seqlen, softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse, cu_seqlens = ctx.saved_tensors
+        qkv_shape = q.shape[:-2] + (3, *q.shape[-2:])
+        dqkv = torch.empty(qkv_shape, dtype=q.dtype, device=q.device)
+        _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dqkv[:, 0], dqkv[:, 1], dqkv[:, 2],
+                                    cu_seqlens, cu_seqlens, ctx.max_seqlen, ctx.max_seqlen, ctx.dropout_p,
+                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+        dqkv = dqkv[..., :dout.shape[-1]]
+        return dqkv, None, None, None, None, None, None, None
+
+
+class FlashAttnKVPackedFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, kv, dropout_p, softmax_scale, causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = q.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
+            q, kv[:, :, 0], kv[:, :, 1], dropout_p, softmax_scale, causal=causal,
+            return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
+        ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse = ctx.saved_tensors
+        dq = torch.empty_like(q)
+        kv_shape = k.shape[:-2] + (2, *k.shape[-2:])
+        dkv = torch.empty(kv_shape, dtype=k.dtype, device=k.device)
+        _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dkv[:, :, 0], dkv[:, :, 1], ctx.dropout_p,
+                             ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+        dq = dq[..., :dout.shape[-1]]
+        dkv = dkv[..., :dout.shape[-1]]
+        return dq, dkv, None, None, None, None, None
+
+
+class FlashAttnVarlenKVPackedFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
+                causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = q.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
+            q, kv[:, 0], kv[:, 1], cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
+            softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens_q, cu_seqlens_k)
+        ctx.dropout_p, ctx.max_seqlen_q, ctx.max_seqlen_k = dropout_p, max_seqlen_q, max_seqlen_k
+        ctx.softmax_scale, ctx.causal, ctx.mask = softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k = ctx.saved_tensors
+        dq = torch.empty_like(q)
+        kv_shape = k.shape[:-2] + (2, *k.shape[-2:])
+        dkv = torch.empty(kv_shape, dtype=k.dtype, device=k.device)
+        _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dq, dkv[:, 0], dkv[:, 1], cu_seqlens_q,
+                                    cu_seqlens_k, ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p,
+                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+        dq = dq[..., :dout.shape[-1]]
+        dkv = dkv[..., :dout.shape[-1]]
+        return dq, dkv, None, None, None, None, None, None, None, None, None
+
+
+class FlashAttnFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, dropout_p, softmax_scale, causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = q.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
+            q, k, v, dropout_p, softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0,
+            mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
+        ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse = ctx.saved_tensors
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, ctx.dropout_p, ctx.softmax_scale,
+                             ctx.causal, mask=ctx.mask)
+        dq = dq[..., :dout.shape[-1]]
+        dk = dk[..., :dout.shape[-1]]
+        dv = dv[..., :dout.shape[-1]]
+        return dq, dk, dv, None, None, None, None, None
+
+
+class FlashAttnVarlenFunc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
+                causal, return_softmax, mask=_NO_MASK):
+        if softmax_scale is None:
+            softmax_scale = q.shape[-1] ** (-0.5)
+        out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
+            q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
+            causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens_q, cu_seqlens_k)
+        ctx.dropout_p, ctx.max_seqlen_q, ctx.max_seqlen_k = dropout_p, max_seqlen_q, max_seqlen_k
+        ctx.softmax_scale, ctx.causal, ctx.mask = softmax_scale, causal, mask
+        return out if not return_softmax else (out, softmax_lse, S_dmask)
+
+    @staticmethod
+    def backward(ctx, dout, *args):
+        q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k = ctx.saved_tensors
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
+                                    ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p, ctx.softmax_scale,
+                                    ctx.causal, mask=ctx.mask)
+        dq = dq[..., :dout.shape[-1]]
+        dk = dk[..., :dout.shape[-1]]
+        dv = dv[..., :dout.shape[-1]]
+        return dq, dk, dv, None, None, None, None, None, None, None, None, None
+
+
+# ----------------------------------------------------------------------------------------------------
+# public functions (flash_attn_interface.py:282-492) -- positional order and defaults as the reference
+# ----------------------------------------------------------------------------------------------------
+def _mk_mask(window_size, flashmask, force_generic=False):
+    if tuple(window_size) == (-1, -1) and flashmask is None and not force_generic:
+        return _NO_MASK
+    return _Mask(window=window_size, flashmask=flashmask, force_generic=force_generic)
+
+
+def flash_attn_qkvpacked_func(qkv, dropout_p=0.0, softmax_scale=None, causal=False, return_attn_probs=False, *,
+                              window_size=(-1, -1), flashmask=None, _force_generic=False):
+    """qkv: (batch_size, seqlen, 3, nheads, headdim).  Returns out (batch_size, seqlen, nheads, headdim)
+    [+ softmax_lse (batch_size, nheads, seqlen) fp32, S_dmask] (reference :282-311)."""
+    return FlashAttnQKVPackedFunc.apply(qkv, dropout_p, softmax_scale, causal, return_attn_probs,
+                                        _mk_mask(window_size, flashmask, _force_generic))
+
+
+def flash_attn_kvpacked_func(q, kv, dropout_p=0.0, softmax_scale=None, causal=False, return_attn_probs=False, *,
+                             window_size=(-1, -1), flashmask=None, _force_generic=False):
+    """q: (batch_size, seqlen_q, nheads, headdim); kv: (batch_size, seqlen_k, 2, nheads_k, headdim) with
+    nheads % nheads_k == 0 (MQA/GQA) (reference :314-342)."""
+    return FlashAttnKVPackedFunc.apply(q, kv, dropout_p, softmax_scale, causal, return_attn_probs,
+                                       _mk_mask(window_size, flashmask, _force_generic))
+
+
+def flash_attn_func(q, k, v, dropout_p=0.0, softmax_scale=None, causal=False, return_attn_probs=False, *,
+                    window_size=(-1, -1), flashmask=None, _force_generic=False):
+    """q: (batch_size, seqlen_q, nheads, headdim); k, v: (batch_size, seqlen_k, nheads_k, headdim)
+    (reference :345-373).  ``causal`` is top-left aligned, as in the reference."""
+    return FlashAttnFunc.apply(q, k, v, dropout_p, softmax_scale, causal, return_attn_probs,
+                               _mk_mask(window_size, flashmask, _force_generic))
+
+
+def flash_attn_varlen_qkvpacked_func(qkv, cu_seqlens, max_seqlen, dropout_p=0.0, softmax_scale=None, causal=False,
+                                     return_attn_probs=False, *, _force_generic=False):
+    """qkv: (total, 3, nheads, headdim); cu_seqlens: (batch_size + 1,) int32 (reference :376-411)."""
+    return FlashAttnVarlenQKVPackedFunc.apply(qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal,
+                                              return_attn_probs, _mk_mask((-1, -1), None, _force_generic))
+
+
+def flash_attn_varlen_kvpacked_func(q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p=0.0,
+                                    softmax_scale=None, causal=False, return_attn_probs=False, *,
+                                    _force_generic=False):
+    """q: (total_q, nheads, headdim); kv: (total_k, 2, nheads_k, headdim) (reference :414-451)."""
+    return FlashAttnVarlenKVPackedFunc.apply(q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
+                                             dropout_p, softmax_scale, causal, return_attn_probs,
+                                             _mk_mask((-1, -1), None, _force_generic))
+
+
+def flash_attn_varlen_func(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p=0.0,
+                           softmax_scale=None, causal=False, return_attn_probs=False, *, window_size=(-1, -1),
+                           _force_generic=False):
+    """q: (total_q, nheads, headdim); k, v: (total_k, nheads_k, headdim); cu_seqlens_*: (batch_size + 1,) int32
+    (reference :454-492)."""
+    return FlashAttnVarlenFunc.apply(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
+                                     softmax_scale, causal, return_attn_probs,
+                                     _mk_mask(window_size, None, _force_generic))
+
+
+def flashmask_attention(q, k, v, startend_row_indices, dropout_p=0.0, softmax_scale=None, causal=False, *,
+                        _force_generic=False):
+    """The fork's FlashMask operator (Paddle ``flashmask_attention``; kernels in csrc/flashmask_v2).
+
+    ``startend_row_indices``: int32 (batch, mask_heads, seqlen_k, {1, 2, 4}) holding, per key column,
+    [lt_start], [lt_start, lt_end] (causal) / [lt_start, ut_end] (non-causal), or
+    [lt_start, lt_end, ut_start, ut_end].  Query row i is masked for column j iff
+    lt_start[j] <= i < lt_end[j] or ut_start[j] <= i < ut_end[j].
+    """
+    n = startend_row_indices.shape[-1]
+    cols = [startend_row_indices[..., i].contiguous() for i in range(n)]
+    if n == 1:
+        fm = (cols[0], None, None, None)
+    elif n == 2:
+        fm = (cols[0], cols[1], None, None) if causal else (cols[0], None, None, cols[1])
+    elif n == 4:
+        fm = (cols[0], cols[1], cols[2], cols[3])
+    else:
+        raise ValueError("startend_row_indices last dim must be 1, 2 or 4")
+    return FlashAttnFunc.apply(q, k, v, dropout_p, softmax_scale, causal, False,
+                               _Mask(flashmask=fm, force_generic=_force_generic))
+
+
+def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None, rotary_sin=None,
+                            cache_seqlens=None, cache_batch_idx=None, cache_leftpad=None, block_table=None,
+                            softmax_scale=None, causal=False, window_size=(-1, -1), softcap=0.0,
+                            rotary_interleaved=True, alibi_slopes=None, num_splits=0, return_softmax_lse=False):
+    """Decode-time attention over a KV cache, upstream signature (the fork only has the capability at C level:
+    csrc/flash_attn_v3/flash.h:96-125 knew_ptr / seqused_k / num_splits / oaccum_ptr, plus the combine kernel).
+
+    q: (batch, seqlen_q, nheads, headdim); k_cache, v_cache: (batch, seqlen_cache, nheads_k, headdim).
+    If ``k``/``v`` are given they are appended IN PLACE at ``cache_seqlens`` before attention.  ``causal`` and
+    ``window_size`` are bottom-right aligned (csrc/flashmask_v2/mask.h:85-118).  ``num_splits=0`` picks the split
+    count with the reference heuristic (csrc/flashmask_v2/heuristics.h:22-59); partial results are merged by the
+    LSE-combine kernel.  Inference only (no autograd).
+    """
+    for name, val in (("rotary_cos", rotary_cos), ("rotary_sin", rotary_sin), ("cache_batch_idx", cache_batch_idx),
+                      ("cache_leftpad", cache_leftpad), ("block_table", block_table), ("alibi_slopes", alibi_slopes)):
+        if val is not None:
+            raise NotImplementedError(f"flash_attn_with_kvcache: {name} is not implemented (SURVEY.md 8(f) rank 4)")
+    if softcap != 0.0:
+        raise NotImplementedError("flash_attn_with_kvcache: softcap is not implemented (SURVEY.md 8(f) rank 4)")
+    q, k_cache, v_cache = [_maybe_contiguous(x) for x in (q, k_cache, v_cache)]
+    b, sq, h, d = q.shape
+    sk, h_k = k_cache.shape[1], k_cache.shape[2]
+    if d % 8 != 0:
+        raise RuntimeError("flash_attn_with_kvcache: head dimension must be a multiple of 8")
+    if softmax_scale is None:
+        softmax_scale = d ** (-0.5)
+    lib = _capi.load()
+    stream = _capi.stream_ptr(q.device)
+    if cache_seqlens is not None and isinstance(cache_seqlens, int):
+        cache_seqlens = torch.full((b,), cache_seqlens, dtype=torch.int32, device=q.device)
+    with torch.cuda.device(q.device):
+        seqused = cache_seqlens
+        if k is not None:
+            assert v is not None
+            k, v = _maybe_contiguous(k), _maybe_contiguous(v)
+            s_new = k.shape[1]
+            is_bf16 = 1 if q.dtype == torch.bfloat16 else 0
+            for new, cache in ((k, k_cache), (v, v_cache)):  # K and V may have different strides: one call each
+                _capi.check(lib.fa_b200_append_kv(
+                    new.data_ptr(), new.data_ptr(), cache.data_ptr(), cache.data_ptr(), ptr(cache_seqlens),
+                    b, s_new, sk, h_k, d, is_bf16, new.stride(0), new.stride(1), new.stride(2),
+                    cache.stride(0), cache.stride(1), cache.stride(2), stream), "fa_b200_append_kv")
+            seqused = (cache_seqlens + s_new) if cache_seqlens is not None else \
+                torch.full((b,), s_new, dtype=torch.int32, device=q.device)
+        p = new_params(q.dtype)
+        out = torch.empty_like(q)
+        lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
+        p.q, p.k, p.v, p.o = tdesc(q), tdesc(k_cache), tdesc(v_cache), tdesc(out)
+        p.softmax_lse = lse.data_ptr()
+        p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
+        p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+        p.softmax_scale = softmax_scale
+        p.is_causal = 1 if causal else 0
+        p.causal_bottom_right = 1
+        p.window_left, p.window_right = window_size
+        p.lse_empty_is_neg_inf = 1
+        if seqused is not None:
+            seqused = seqused.to(torch.int32).contiguous()
+            p.seqused_k = seqused.data_ptr()
+        if num_splits <= 0:
+            num_sm = torch.cuda.get_device_properties(q.device).multi_processor_count
+            num_splits = lib.fa_b200_num_splits(b, h_k, sq * (h // h_k), sk, d, num_sm)
+        p.num_splits = num_splits
+        if num_splits > 1:
+            oaccum = torch.empty((num_splits, b, sq, h, d), dtype=torch.float32, device=q.device)
+            lseaccum = torch.empty((num_splits, b, h, sq), dtype=torch.float32, device=q.device)
+            p.oaccum, p.lseaccum = oaccum.data_ptr(), lseaccum.data_ptr()
+            _capi.check(lib.fa_b200_fwd_splitkv(p, stream), "fa_b200_fwd_splitkv")
+            _capi.check(lib.fa_b200_fwd_combine(p, stream), "fa_b200_fwd_combine")
+        else:
+            _capi.check(lib.fa_b200_fwd_splitkv(p, stream), "fa_b200_fwd_splitkv")
+    return (out, lse) if return_softmax_lse else out
