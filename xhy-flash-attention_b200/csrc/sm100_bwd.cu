@@ -1,0 +1,594 @@
+// sm100_bwd.cu -- the tcgen05 / TMEM / TMA backward kernels (sm_100a).
+//
+// Same mathematics as the reference's compute_dq_dk_dv_1colblock (csrc/flash_attn/src/flash_bwd_kernel.h:427-1113):
+//   S = Q K^T, P = exp2(S * scale_log2 - LSE * log2e), dP = dO V^T, dS = P o (dP - dPsum),
+//   dV += P^T dO, dK += dS^T Q (x scale), dQ += dS K (x scale, fp32 accumulation across key blocks),
+// preceded by dPsum = rowsum(dO o O) (:112-188) and followed by the fp32 -> 16-bit dQ conversion (:232-310).
+//
+// Blackwell structure.  One CTA owns one 128-key block of one (batch, kv-head) and loops over the query blocks of
+// every q-head of the group, so dK/dV accumulate in TMEM with no atomics and GQA needs no expanded buffers.
+// Everything is computed TRANSPOSED (keys on TMEM lanes) so that P^T and dS^T can feed the dV / dK MMAs straight
+// from TMEM (an A operand in TMEM cannot be transposed):
+//   warp 12   : MMA issuer   S^T = K Q^T, dP^T = V dO^T (SS), dV += P^T dO, dK += dS^T Q (TS), dQ = dS K (SS, dS^T in smem)
+//   warp 13   : producer     TMA loads of K, V (once) and Q (2 stages), dO; LSE*log2e and dPsum rows into smem
+//   warps 0-7 : compute      two warpgroups, each owns 64 of the 128 query columns of S^T / dP^T
+//   warps 8-11: dQ reducers  TMEM -> registers -> smem -> cp.reduce.async.bulk (fp32 add) into the dq_accum workspace
+// TMEM columns: S^T/P^T [0,128)  dV [128,128+HD)  dP^T/dS^T/dQ [256,384)  dK [384,384+HD).
+//
+// dq_accum layout (a private workspace): tiles of 128 rows; per tile HD/32 chunks; a chunk is 128 rows x 32 floats
+// (16 KiB, the unit of one bulk reduce-add) whose 16-byte groups are XOR-swizzled with (row % 8).
+#include <math_constants.h>
+#include <type_traits>
+
+#include "common.h"
+#include "sm100.cuh"
+
+namespace fa {
+namespace {
+
+using namespace sm100;
+
+constexpr int kB = 128;            // query rows per block == keys per block
+constexpr int kBwdThreads = 512;   // 16 warps (the last two idle; they only pad the register-budget warpgroup)
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct BwdTma {
+  CUtensorMap q, k, v, dout;
+};
+
+template <int HD> struct BwdSmem {
+  static constexpr int kTile = kB * HD * 2;              // one 128 x HD 16-bit tile
+  static constexpr int kK = 0;
+  static constexpr int kV = kK + kTile;
+  static constexpr int kQ = kV + kTile;                  // 2 stages
+  static constexpr int kDO = kQ + 2 * kTile;
+  static constexpr int kDS = kDO + kTile;                // dS^T: 2 halves x (128 keys x 128 bytes)
+  static constexpr int kDQ = kDS + kB * kB * 2;          // dQ staging chunk: 128 rows x 32 floats
+  static constexpr int kVec = kDQ + kB * 32 * 4;         // [2 stages][lse2 | dpsum][128] floats
+  static constexpr int kBar = kVec + 2 * 2 * kB * 4;
+  static constexpr int kNumBars = 16;
+  static constexpr int kTmemSlot = kBar + kNumBars * 8;
+  static constexpr int kTotal = kTmemSlot + 16;
+  static constexpr int kDynBytes = kTotal + 1024;
+};
+
+enum BwdBar {
+  BB_KV_FULL = 0, BB_Q_FULL = 1 /*2*/, BB_Q_EMPTY = 3 /*2*/, BB_DO_FULL = 5, BB_DO_EMPTY = 6, BB_S_FULL = 7, BB_P_FULL = 8,
+  BB_DP_FULL = 9, BB_DS_FULL = 10, BB_DQ_FULL = 11, BB_DQ_EMPTY = 12, BB_DKV_FULL = 13
+};
+
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+// What one CTA works on: key block n0 of (batch bi, kv-head hk); q-heads [hq0, hq1); per head query blocks [m_lo, m_hi).
+struct BwdTile {
+  int bi, hk, ho, n0;
+  int hq0, hq1;
+  int sq, sk, q_row0, k_row0, q_b, k_b;
+  int m_lo, m_hi;
+  int acc_tile0;     // first dq_accum tile of this batch element (before head offset)
+  int acc_tiles_per_head;
+};
+
+__device__ __forceinline__ bool bwd_decode(const Params &p, BwdTile &t) {
+  // grid: x = key block (descending work with ascending index for causal), y = output head, z = batch
+  t.bi = blockIdx.z;
+  t.ho = blockIdx.y;
+  const int g = p.h / p.h_k;
+  if (p.dkv_expanded) { t.hk = t.ho / g; t.hq0 = t.ho; t.hq1 = t.ho + 1; }
+  else { t.hk = t.ho; t.hq0 = t.ho * g; t.hq1 = t.ho * g + g; }
+  bool qb, kb;
+  seq_bounds(p, t.bi, t.q_row0, t.sq, t.k_row0, t.sk, qb, kb);
+  t.q_b = qb ? t.bi : 0;
+  t.k_b = kb ? t.bi : 0;
+  t.n0 = blockIdx.x * kB;
+  if (t.n0 >= t.sk) return false;
+  const int shift = t.sk - t.sq;
+  const int shiftc = p.causal_bottom_right ? shift : 0;
+  // rows that can see any key of [n0, n0 + 128): causal: row >= col - shiftc; window_right: row >= col - shift - wr;
+  // window_left: row <= col - shift + wl
+  int rlo = 0, rhi = t.sq;
+  const int c_last = min(t.n0 + kB, t.sk) - 1;
+  if (p.is_causal) rlo = max(rlo, t.n0 - shiftc);
+  if (p.window_right >= 0) rlo = max(rlo, t.n0 - shift - p.window_right);
+  if (p.window_left >= 0) rhi = min(rhi, c_last - shift + p.window_left + 1);
+  t.m_lo = rlo / kB;
+  t.m_hi = (max(rhi, 0) + kB - 1) / kB;
+  if (t.m_hi < t.m_lo) t.m_hi = t.m_lo;
+  if (p.cu_seqlens_q && !p.varlen_padded_input) {
+    t.acc_tile0 = (p.cu_seqlens_q[t.bi] + kB * t.bi) / kB;
+    t.acc_tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+  } else {
+    t.acc_tiles_per_head = p.seqlen_q_rounded / kB;
+    t.acc_tile0 = t.bi * p.h * t.acc_tiles_per_head;  // batch-major: (b, h, tile)
+  }
+  return true;
+}
+
+// index of the dq_accum tile for (head hq, query block m)
+__device__ __forceinline__ int64_t acc_tile_index(const Params &p, const BwdTile &t, int hq, int m) {
+  if (p.cu_seqlens_q && !p.varlen_padded_input) return (int64_t)hq * t.acc_tiles_per_head + t.acc_tile0 + m;
+  return (int64_t)t.acc_tile0 + (int64_t)hq * t.acc_tiles_per_head + m;
+}
+
+template <int HD, bool kBf16>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) {
+  using L = BwdSmem<HD>;
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  auto bar = [&](int i) { return sbase + L::kBar + i * 8; };
+  uint32_t *tmem_slot = (uint32_t *)(smem + L::kTmemSlot);
+  float *vec = (float *)(smem + L::kVec);  // [stage][0: lse*log2e, 1: dpsum][128]
+
+  BwdTile t;
+  const bool live = bwd_decode(p, t);
+  if (!live) return;  // uniform for the whole CTA
+  const int nm = t.m_hi - t.m_lo;
+  const int n_it = (t.hq1 - t.hq0) * nm;
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar(BB_KV_FULL), 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(bar(BB_Q_FULL + s), 1); mbar_init(bar(BB_Q_EMPTY + s), 1); }
+    mbar_init(bar(BB_DO_FULL), 1); mbar_init(bar(BB_DO_EMPTY), 1);
+    mbar_init(bar(BB_S_FULL), 1); mbar_init(bar(BB_P_FULL), 256);
+    mbar_init(bar(BB_DP_FULL), 1); mbar_init(bar(BB_DS_FULL), 256);
+    mbar_init(bar(BB_DQ_FULL), 1); mbar_init(bar(BB_DQ_EMPTY), 128);
+    mbar_init(bar(BB_DKV_FULL), 1);
+    fence_mbar_init();
+  }
+  if (warp == 12) tmem_alloc<512>(smem_u32(tmem_slot));
+  if (warp == 13 && lane == 0) {
+    tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v); tma_prefetch_desc(&tm.dout);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  constexpr int kHalves = HD / 64;
+  constexpr uint32_t kHalfBytes = kB * 128;
+  constexpr uint32_t TS_ = 0, TDV = 128, TDP = 256, TDK = 384;  // TMEM column map
+  const float scale_log2 = p.softmax_scale * kLog2e;
+
+  if (warp >= 12) {
+    setmaxnreg_dec<96>();
+    if (warp == 13) {
+      // ======================= producer =======================
+      if (lane == 0 && n_it > 0) {
+        mbar_expect_tx(bar(BB_KV_FULL), 2 * L::kTile);
+#pragma unroll
+        for (int hf = 0; hf < kHalves; ++hf) {
+          tma_load_4d(sbase + L::kK + hf * kHalfBytes, &tm.k, bar(BB_KV_FULL), hf * 64, t.hk, t.k_row0 + t.n0, t.k_b);
+          tma_load_4d(sbase + L::kV + hf * kHalfBytes, &tm.v, bar(BB_KV_FULL), hf * 64, t.hk, t.k_row0 + t.n0, t.k_b);
+        }
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+        mbar_wait(bar(BB_Q_EMPTY + st), ((it >> 1) & 1) ^ 1);
+        const float *lse = p.softmax_lse + ((int64_t)t.bi * p.h + hq) * p.seqlen_q;
+        const float *dps = p.softmax_d + ((int64_t)t.bi * p.h + hq) * p.seqlen_q_rounded;
+#pragma unroll
+        for (int i = lane; i < kB; i += 32) {
+          const int row = m * kB + i;
+          float l = CUDART_INF_F, dsum = 0.f;
+          if (row < t.sq) {
+            l = lse[row];
+            l = isinf(l) ? CUDART_INF_F : l * kLog2e;
+            dsum = dps[row];
+          }
+          vec[(st * 2 + 0) * kB + i] = l;
+          vec[(st * 2 + 1) * kB + i] = dsum;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          mbar_expect_tx(bar(BB_Q_FULL + st), L::kTile);
+#pragma unroll
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_load_4d(sbase + L::kQ + st * L::kTile + hf * kHalfBytes, &tm.q, bar(BB_Q_FULL + st), hf * 64, hq,
+                        t.q_row0 + m * kB, t.q_b);
+          mbar_wait(bar(BB_DO_EMPTY), (it & 1) ^ 1);
+          mbar_expect_tx(bar(BB_DO_FULL), L::kTile);
+#pragma unroll
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_load_4d(sbase + L::kDO + hf * kHalfBytes, &tm.dout, bar(BB_DO_FULL), hf * 64, hq, t.q_row0 + m * kB,
+                        t.q_b);
+        }
+        __syncwarp();
+      }
+    } else if (warp == 12 && lane == 0 && n_it > 0) {
+      // ======================= MMA issuer =======================
+      constexpr uint32_t idesc_st = make_idesc(kBf16, kB, kB, false, false);   // S^T, dP^T: K-major x K-major
+      constexpr uint32_t idesc_kv = make_idesc(kBf16, kB, HD, false, true);    // dV, dK: A in TMEM, B MN-major
+      constexpr uint32_t idesc_dq = make_idesc(kBf16, kB, HD, true, true);     // dQ: A (dS^T) MN-major, B (K) MN-major
+      const uint32_t sK = sbase + L::kK, sV = sbase + L::kV, sDO = sbase + L::kDO, sDS = sbase + L::kDS;
+      auto kmajor_pair = [&](uint32_t d_col, uint32_t a_base, uint32_t b_base) {
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) {
+          const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
+          umma_ss(tmem + d_col, make_sdesc_sw128(a_base + off, 16, 1024), make_sdesc_sw128(b_base + off, 16, 1024),
+                  idesc_st, k > 0);
+        }
+      };
+      auto tmem_a_mn_b = [&](uint32_t d_col, uint32_t a_col, uint32_t b_base, bool accumulate) {
+#pragma unroll
+        for (int k = 0; k < kB / 16; ++k) {
+          const uint32_t a = tmem + a_col + (k < 4 ? k * 8 : 64 + (k - 4) * 8);  // each compute warpgroup packs into its own half
+          umma_ts(tmem + d_col, a, make_sdesc_sw128(b_base + k * 2048, kHalfBytes, 1024), idesc_kv,
+                  (accumulate || k > 0) ? 1u : 0u);
+        }
+      };
+      mbar_wait(bar(BB_KV_FULL), 0);
+      mbar_wait(bar(BB_Q_FULL + 0), 0);
+      tc_fence_after();
+      kmajor_pair(TS_, sK, sbase + L::kQ);
+      umma_commit(bar(BB_S_FULL));
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t sQ = sbase + L::kQ + st * L::kTile;
+        mbar_wait(bar(BB_DO_FULL), it & 1);
+        if (it > 0) mbar_wait(bar(BB_DQ_EMPTY), (it - 1) & 1);   // dQ(it-1) has left TMEM: the dP region is free
+        tc_fence_after();
+        kmajor_pair(TDP, sV, sDO);
+        umma_commit(bar(BB_DP_FULL));
+        mbar_wait(bar(BB_P_FULL), it & 1);
+        tc_fence_after();
+        tmem_a_mn_b(TDV, TS_, sDO, it > 0);
+        umma_commit(bar(BB_DO_EMPTY));
+        if (it + 1 < n_it) {
+          mbar_wait(bar(BB_Q_FULL + (st ^ 1)), ((it + 1) >> 1) & 1);
+          tc_fence_after();
+          kmajor_pair(TS_, sK, sbase + L::kQ + (st ^ 1) * L::kTile);
+          umma_commit(bar(BB_S_FULL));
+        }
+        mbar_wait(bar(BB_DS_FULL), it & 1);
+        tc_fence_after();
+        tmem_a_mn_b(TDK, TDP, sQ, it > 0);
+        umma_commit(bar(BB_Q_EMPTY + st));
+#pragma unroll
+        for (int k = 0; k < kB / 16; ++k)
+          umma_ss(tmem + TDP, make_sdesc_sw128(sDS + k * 2048, kHalfBytes, 1024),
+                  make_sdesc_sw128(sK + k * 2048, kHalfBytes, 1024), idesc_dq, k > 0);
+        umma_commit(bar(BB_DQ_FULL));
+      }
+      umma_commit(bar(BB_DKV_FULL));
+    }
+  } else if (warp >= 8) {
+    // ======================= dQ reducers =======================
+    setmaxnreg_dec<120>();
+    const int r = (warp % 4) * 32 + lane;
+    const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
+    const int tid = threadIdx.x - 256;
+    const int n_chunks = p.d_rounded / 32 < HD / 32 ? p.d_rounded / 32 : HD / 32;
+    uint8_t *stg = smem + L::kDQ;
+    for (int it = 0; it < n_it; ++it) {
+      const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+      float *gtile = p.dq_accum + acc_tile_index(p, t, hq, m) * (int64_t)(p.d_rounded / 32) * (kB * 32);
+      mbar_wait(bar(BB_DQ_FULL), it & 1);
+      tc_fence_after();
+      for (int c = 0; c < n_chunks; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tmem + lane_base + TDP + c * 32, v);
+        tmem_wait_ld();
+        if (c == n_chunks - 1) {
+          tc_fence_before();
+          mbar_arrive(bar(BB_DQ_EMPTY));
+        }
+        if (tid == 0) bulk_wait_read<0>();          // the previous chunk has been read out of the staging buffer
+        named_bar_sync(3, 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4 *>(stg + r * 128 + ((j ^ (r & 7)) * 16)) =
+              make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_proxy_async_smem();
+        named_bar_sync(4, 128);
+        if (tid == 0) {
+          bulk_reduce_add_f32(gtile + c * (kB * 32), smem_u32(stg), kB * 32 * 4);
+          bulk_commit();
+        }
+      }
+    }
+    if (tid == 0) bulk_wait<0>();
+  } else {
+    // ======================= compute warpgroups =======================
+    setmaxnreg_inc<144>();
+    const int wg = warp / 4;
+    const int r = (warp % 4) * 32 + lane;          // key row inside the block == TMEM lane
+    const int col = t.n0 + r;                      // key index
+    const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
+    const uint32_t tS = tmem + lane_base + TS_ + wg * 64, tP = tmem + lane_base + TS_ + wg * 64;
+    const uint32_t tDP = tmem + lane_base + TDP + wg * 64, tDS = tmem + lane_base + TDP + wg * 64;
+    uint8_t *ds_row = smem + L::kDS + wg * kHalfBytes + r * 128;
+    const int shift = t.sk - t.sq;
+    const int shiftc = p.causal_bottom_right ? shift : 0;
+    for (int it = 0; it < n_it; ++it) {
+      const int st = it & 1;
+      const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+      const int m0 = m * kB;
+      const MaskCtx mc = make_mask_ctx(p, t.bi, hq, t.sq, t.sk);
+      const bool full = (t.n0 + kB <= t.sk) && (!mc.causal || t.n0 + kB - 1 <= m0 + shiftc) &&
+                        (mc.wr < 0 || t.n0 + kB - 1 <= m0 + shift + mc.wr) &&
+                        (mc.wl < 0 || t.n0 >= m0 + kB - 1 + shift - mc.wl) && (mc.lts == nullptr);
+      const float *lse2 = vec + (st * 2 + 0) * kB + wg * 64;
+      const float *dpsum = vec + (st * 2 + 1) * kB + wg * 64;
+      mbar_wait(bar(BB_Q_FULL + st), (it >> 1) & 1);   // LSE / dPsum rows of this query block are in smem
+      mbar_wait(bar(BB_S_FULL), it & 1);
+      tc_fence_after();
+      float pr[64];
+#pragma unroll
+      for (int c2 = 0; c2 < 2; ++c2) {
+        uint32_t s[32];
+        tmem_ld32(tS + c2 * 32, s);
+        tmem_wait_ld();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const int qi = c2 * 32 + i;
+          float p0 = ex2f(fmaf(__uint_as_float(s[i]), scale_log2, -lse2[qi]));
+          float p1 = ex2f(fmaf(__uint_as_float(s[i + 1]), scale_log2, -lse2[qi + 1]));
+          if (!full) {
+            if (is_masked(mc, m0 + wg * 64 + qi, col)) p0 = 0.f;
+            if (is_masked(mc, m0 + wg * 64 + qi + 1, col)) p1 = 0.f;
+          }
+          pr[qi] = p0; pr[qi + 1] = p1;
+          pk[i / 2] = pack2<kBf16>(p0, p1);
+        }
+        tmem_st16(tP + c2 * 16, pk);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(bar(BB_P_FULL));
+
+      mbar_wait(bar(BB_DP_FULL), it & 1);
+      if (it > 0) mbar_wait(bar(BB_DQ_FULL), (it - 1) & 1);  // dQ(it-1) no longer reads the dS^T smem tile
+      tc_fence_after();
+#pragma unroll
+      for (int c2 = 0; c2 < 2; ++c2) {
+        uint32_t dp[32];
+        tmem_ld32(tDP + c2 * 32, dp);
+        tmem_wait_ld();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const int qi = c2 * 32 + i;
+          const float d0 = pr[qi] * (__uint_as_float(dp[i]) - dpsum[qi]);
+          const float d1 = pr[qi + 1] * (__uint_as_float(dp[i + 1]) - dpsum[qi + 1]);
+          pk[i / 2] = pack2<kBf16>(d0, d1);
+        }
+        tmem_st16(tDS + c2 * 16, pk);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4 *>(ds_row + (((c2 * 4 + j) ^ (r & 7)) * 16)) =
+              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(bar(BB_DS_FULL));
+    }
+    // ---------------- epilogue: dK (x scale), dV ----------------
+    const bool row_ok = col < t.sk;
+    T *dk_row = (T *)p.dk.ptr + (int64_t)t.k_b * p.dk.batch_stride + (int64_t)(t.k_row0 + col) * p.dk.row_stride +
+                (int64_t)t.ho * p.dk.head_stride;
+    T *dv_row = (T *)p.dv.ptr + (int64_t)t.k_b * p.dv.batch_stride + (int64_t)(t.k_row0 + col) * p.dv.row_stride +
+                (int64_t)t.ho * p.dv.head_stride;
+    if (n_it > 0) {
+      mbar_wait(bar(BB_DKV_FULL), 0);
+      tc_fence_after();
+    }
+    constexpr int kColsPerWg = HD / 2;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      T *dst = which == 0 ? dv_row : dk_row;
+      const float mul = which == 0 ? 1.f : p.softmax_scale;
+#pragma unroll
+      for (int c = 0; c < kColsPerWg / 32; ++c) {
+        uint32_t v[32];
+        const int c0 = wg * kColsPerWg + c * 32;
+        if (n_it > 0) {
+          tmem_ld32(tmem + lane_base + (which == 0 ? TDV : TDK) + c0, v);
+          tmem_wait_ld();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = 0;
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (c0 + j * 8 < p.d) {
+              uint4 o;
+              o.x = pack2<kBf16>(__uint_as_float(v[j * 8 + 0]) * mul, __uint_as_float(v[j * 8 + 1]) * mul);
+              o.y = pack2<kBf16>(__uint_as_float(v[j * 8 + 2]) * mul, __uint_as_float(v[j * 8 + 3]) * mul);
+              o.z = pack2<kBf16>(__uint_as_float(v[j * 8 + 4]) * mul, __uint_as_float(v[j * 8 + 5]) * mul);
+              o.w = pack2<kBf16>(__uint_as_float(v[j * 8 + 6]) * mul, __uint_as_float(v[j * 8 + 7]) * mul);
+              *reinterpret_cast<uint4 *>(dst + c0 + j * 8) = o;
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 12) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
+// pre: dPsum[b, h, row] = sum_d dO * O  (fp32, (b, h, seqlen_q_rounded), 0 for padded rows).  One warp per row.
+// (csrc/flash_attn/src/flash_bwd_kernel.h:112-188)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) bwd_dpsum_kernel(const Params p) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int hq = blockIdx.y, bi = blockIdx.z;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= p.seqlen_q_rounded) return;
+  int q_row0, sq, k_row0, sk;
+  bool qb, kb;
+  seq_bounds(p, bi, q_row0, sq, k_row0, sk, qb, kb);
+  float acc = 0.f;
+  if (row < sq) {
+    const T *o = (const T *)p.o.ptr + (qb ? bi : 0) * p.o.batch_stride + (int64_t)(q_row0 + row) * p.o.row_stride +
+                 (int64_t)hq * p.o.head_stride;
+    const T *g = (const T *)p.dout.ptr + (qb ? bi : 0) * p.dout.batch_stride +
+                 (int64_t)(q_row0 + row) * p.dout.row_stride + (int64_t)hq * p.dout.head_stride;
+    for (int e = lane * 8; e < p.d; e += 256) {
+      const uint4 a = *reinterpret_cast<const uint4 *>(o + e);
+      const uint4 b = *reinterpret_cast<const uint4 *>(g + e);
+      const T *ae = reinterpret_cast<const T *>(&a);
+      const T *be = reinterpret_cast<const T *>(&b);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc = fmaf((float)ae[i], (float)be[i], acc);
+    }
+#pragma unroll
+    for (int o2 = 16; o2 > 0; o2 >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o2);
+  }
+  if (lane == 0) p.softmax_d[((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// post: dQ = T(scale * dq_accum), un-tiling the accumulator layout.  One thread per 8 output elements.
+// (csrc/flash_attn/src/flash_bwd_kernel.h:232-310)
+// ------------------------------------------------------------------------------------------------
+template <typename T, bool kBf16>
+__global__ void __launch_bounds__(256) bwd_convert_dq_kernel(const Params p) {
+  const int hq = blockIdx.y, bi = blockIdx.z;
+  int q_row0, sq, k_row0, sk;
+  bool qb, kb;
+  seq_bounds(p, bi, q_row0, sq, k_row0, sk, qb, kb);
+  const int d8 = p.d / 8;
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  const int row = idx / d8, c8 = idx % d8;
+  if (row >= sq) return;
+  int64_t tile;
+  if (p.cu_seqlens_q && !p.varlen_padded_input) {
+    const int tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+    tile = (int64_t)hq * tiles_per_head + (p.cu_seqlens_q[bi] + kB * bi) / kB + row / kB;
+  } else {
+    const int tiles_per_head = p.seqlen_q_rounded / kB;
+    tile = ((int64_t)bi * p.h + hq) * tiles_per_head + row / kB;
+  }
+  const int r = row % kB, col = c8 * 8;
+  const float *chunk = p.dq_accum + (tile * (p.d_rounded / 32) + col / 32) * (int64_t)(kB * 32) + r * 32;
+  const int g0 = (col % 32) / 4;  // 16-byte group inside the 32-float row; two consecutive groups
+  const float4 a = *reinterpret_cast<const float4 *>(chunk + ((g0 ^ (r & 7)) * 4));
+  const float4 b = *reinterpret_cast<const float4 *>(chunk + (((g0 + 1) ^ (r & 7)) * 4));
+  const float s = p.softmax_scale;
+  uint4 o;
+  o.x = pack2<kBf16>(a.x * s, a.y * s); o.y = pack2<kBf16>(a.z * s, a.w * s);
+  o.z = pack2<kBf16>(b.x * s, b.y * s); o.w = pack2<kBf16>(b.z * s, b.w * s);
+  T *dq = (T *)p.dq.ptr + (qb ? bi : 0) * p.dq.batch_stride + (int64_t)(q_row0 + row) * p.dq.row_stride +
+          (int64_t)hq * p.dq.head_stride;
+  *reinterpret_cast<uint4 *>(dq + col) = o;
+}
+
+void sanitize_b(TmaDesc4 &d) {
+  for (int i = 1; i < 4; ++i)
+    if (d.dims[i] == 1) d.strides[i - 1] = 16;
+}
+TmaDesc4 bdesc(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch) {
+  TmaDesc4 x;
+  x.ptr = t.ptr;
+  x.dims[0] = (uint64_t)d; x.dims[1] = (uint64_t)heads; x.dims[2] = (uint64_t)rows; x.dims[3] = (uint64_t)batch;
+  x.strides[0] = (uint64_t)t.head_stride * 2; x.strides[1] = (uint64_t)t.row_stride * 2;
+  x.strides[2] = (uint64_t)t.batch_stride * 2;
+  x.box[0] = 64; x.box[1] = 1; x.box[2] = kB; x.box[3] = 1;
+  sanitize_b(x);
+  return x;
+}
+bool tma_ok_b(const fa_b200_tensor &t, int heads, int batch) {
+  if (((uintptr_t)t.ptr & 15) != 0) return false;
+  if (t.row_stride % 8 != 0 || t.row_stride <= 0) return false;
+  if (heads > 1 && (t.head_stride % 8 != 0 || t.head_stride <= 0)) return false;
+  if (batch > 1 && (t.batch_stride % 8 != 0 || t.batch_stride <= 0)) return false;
+  return true;
+}
+bool out_ok(const fa_b200_tensor &t) {
+  return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
+}
+
+template <int HD, bool kBf16> void launch_bwd(const Params &p, cudaStream_t s) {
+  using L = BwdSmem<HD>;
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
+  BwdTma tm;
+  tm.q = make_tma_4d(bdesc(p.q, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b));
+  tm.dout = make_tma_4d(bdesc(p.dout, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b));
+  tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
+  tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
+  // 1. dPsum
+  {
+    dim3 grid(ceil_div(p.seqlen_q_rounded, 8), p.h, p.b);
+    bwd_dpsum_kernel<T><<<grid, 256, 0, s>>>(p);
+    FA_CUDA(cudaGetLastError());
+    note_launch(2);
+  }
+  // 2. zero the fp32 dQ accumulator
+  {
+    int64_t tiles;
+    if (packed) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+    else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
+    FA_CUDA(cudaMemsetAsync(p.dq_accum, 0, (size_t)tiles * (p.d_rounded / 32) * (kB * 32) * sizeof(float), s));
+  }
+  // 3. main kernel
+  {
+    auto kern = bwd_kernel<HD, kBf16>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
+      attr_set = true;
+    }
+    dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
+    kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm);
+    FA_CUDA(cudaGetLastError());
+    note_launch(2);
+  }
+  // 4. dQ conversion
+  {
+    dim3 grid(ceil_div(p.seqlen_q * (p.d / 8), 256), p.h, p.b);
+    bwd_convert_dq_kernel<T, kBf16><<<grid, 256, 0, s>>>(p);
+    FA_CUDA(cudaGetLastError());
+    note_launch(2);
+  }
+}
+
+}  // namespace
+
+bool sm100_bwd_supported(const Params &p, std::string *why) {
+  auto no = [&](const char *w) { if (why) *why = w; return false; };
+  if (p.d > 128) return no("head_size > 128");
+  if (!p.dq_accum) return no("no dq_accum workspace");
+  if (p.d_rounded != round_up(p.d, 32) || p.seqlen_q_rounded % kB != 0 || p.seqlen_q_rounded < p.seqlen_q)
+    return no("rounded sizes are not the documented ones");
+  if (p.seqused_k) return no("seqused_k");
+  const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
+  if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
+  if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
+  const int nb = packed ? 1 : p.b;
+  if (!tma_ok_b(p.q, p.h, nb) || !tma_ok_b(p.dout, p.h, nb) || !tma_ok_b(p.k, p.h_k, nb) || !tma_ok_b(p.v, p.h_k, nb))
+    return no("strides/alignment not TMA-compatible");
+  if (!out_ok(p.dq) || !out_ok(p.dk) || !out_ok(p.dv) || !out_ok(p.o)) return no("outputs not 16-byte aligned");
+  if (((uintptr_t)p.dq_accum & 127) != 0) return no("dq_accum not 128-byte aligned");
+  return true;
+}
+
+void sm100_bwd(const Params &p, cudaStream_t s) {
+  if (p.d <= 64) {
+    if (p.is_bf16) launch_bwd<64, true>(p, s); else launch_bwd<64, false>(p, s);
+  } else {
+    if (p.is_bf16) launch_bwd<128, true>(p, s); else launch_bwd<128, false>(p, s);
+  }
+}
+
+}  // namespace fa

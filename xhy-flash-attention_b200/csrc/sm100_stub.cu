@@ -5,7 +5,7 @@ namespace fa {
 bool sm100_fwd_supported(const Params &, std::string *) { return false; }
 void sm100_fwd(const Params &, cudaStream_t) {}
 #endif
-#if 1
+#if 0
 bool sm100_bwd_supported(const Params &, std::string *) { return false; }
 void sm100_bwd(const Params &, cudaStream_t) {}
 #endif

@@ -163,8 +163,8 @@ def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p,
     softmax_d = torch.empty((b, h, sq_r), dtype=torch.float32, device=q.device)
     # fp32 dQ accumulator: batch mode (b, h, sq_r, d_r); varlen mode h * (total_q + 128 * b) rows (one tile of
     # slack per sequence so tile-granular reduce-adds never cross sequences)
-    acc_rows = (total_q + 128 * b) * h if varlen else b * h * sq_r
-    dq_accum = torch.empty(round_up(acc_rows, 128) * d_r, dtype=torch.float32, device=q.device)
+    acc_rows = h * round_up(total_q + 128 * b, 128) if varlen else b * h * sq_r
+    dq_accum = torch.empty(acc_rows * d_r, dtype=torch.float32, device=q.device)
     p.q, p.k, p.v, p.o, p.dout, p.dq, p.dk, p.dv = [tdesc(t, packed=varlen) for t in (q, k, v, out, dout, dq, dk, dv)]
     p.softmax_lse, p.softmax_d, p.dq_accum = softmax_lse.data_ptr(), softmax_d.data_ptr(), dq_accum.data_ptr()
     if h != h_k:
