@@ -117,11 +117,16 @@ bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse
                        int64_t rows, int heads, int head_size, int is_bf16, int o_is_fp32,
                        int64_t lse_row_stride, int64_t lse_head_stride, cudaStream_t stream);
 
+/* Per-kernel device timing for bench.py's roofline (CUDA events recorded on the launch stream around the
+ * dominant kernels).  slot 0 = forward kernel, slot 1 = backward main kernel.  Process-wide; not for concurrent use. */
+void fa_b200_profile_enable(int on);
+float fa_b200_profile_last_ms(int slot);
+
 /* Introspection for tests/bench. */
 int fa_b200_abi_version(void);
 /* which kernel family served the last call on this thread: 0 none, 1 generic SIMT, 2 tcgen05 */
 int fa_b200_last_kernel_kind(void);
-/* number of kernels launched by this library on this thread since the last reset */
+/* number of kernels launched by this library (all threads) since the last reset */
 int64_t fa_b200_launch_count(int reset);
 
 #ifdef __cplusplus

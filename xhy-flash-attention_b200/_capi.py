@@ -78,6 +78,10 @@ def load() -> C.CDLL:
     lib.fa_b200_last_kernel_kind.restype = C.c_int
     lib.fa_b200_launch_count.argtypes = [C.c_int]
     lib.fa_b200_launch_count.restype = C.c_int64
+    lib.fa_b200_profile_enable.argtypes = [C.c_int]
+    lib.fa_b200_profile_enable.restype = None
+    lib.fa_b200_profile_last_ms.argtypes = [C.c_int]
+    lib.fa_b200_profile_last_ms.restype = C.c_float
     lib.flash_attn_error.restype = C.c_char_p
     lib.flash_attn_set_error.argtypes = [C.c_char_p]
     if lib.fa_b200_abi_version() != FA_B200_ABI_VERSION:

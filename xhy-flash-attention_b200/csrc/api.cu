@@ -5,6 +5,7 @@
 // There is no CPU path here: every entry point enqueues CUDA kernels on the caller's stream.
 #include <cstring>
 #include <memory>
+#include <atomic>
 #include <mutex>
 
 #include "common.h"
@@ -14,11 +15,23 @@ namespace fa {
 
 static thread_local std::unique_ptr<char[]> tls_error;
 static thread_local int tls_last_kind = 0;
-static thread_local int64_t tls_launches = 0;
+static std::atomic<int64_t> g_launches{0};  // process-wide: backward runs on autograd worker threads
 
 void note_launch(int kind) {
   tls_last_kind = kind;
-  ++tls_launches;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+static bool tls_profile = false;
+static cudaEvent_t tls_events[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+static bool tls_marked[2] = {false, false};
+
+void profile_mark(int slot, bool begin, cudaStream_t s) {
+  if (!tls_profile) return;
+  cudaEvent_t &e = tls_events[slot][begin ? 0 : 1];
+  if (!e) FA_CUDA(cudaEventCreate(&e));
+  FA_CUDA(cudaEventRecord(e, s));
+  if (!begin) tls_marked[slot] = true;
 }
 
 struct DevInfo { int sm_count; int cc_major; int cc_minor; };
@@ -107,11 +120,22 @@ void flash_attn_set_error(const char *msg) {
 
 const char *flash_attn_error(void) { return fa::tls_error ? fa::tls_error.get() : ""; }
 
+void fa_b200_profile_enable(int on) { fa::tls_profile = on != 0; fa::tls_marked[0] = fa::tls_marked[1] = false; }
+
+// elapsed device time (ms) of the last forward kernel (slot 0) / backward main kernel (slot 1) launched on this
+// thread while profiling was enabled; -1 if none.  Blocks until that kernel has finished.
+float fa_b200_profile_last_ms(int slot) {
+  if (slot < 0 || slot > 1 || !fa::tls_marked[slot]) return -1.f;
+  float ms = -1.f;
+  if (cudaEventSynchronize(fa::tls_events[slot][1]) != cudaSuccess) return -1.f;
+  if (cudaEventElapsedTime(&ms, fa::tls_events[slot][0], fa::tls_events[slot][1]) != cudaSuccess) return -1.f;
+  return ms;
+}
+
 int fa_b200_abi_version(void) { return FA_B200_ABI_VERSION; }
 int fa_b200_last_kernel_kind(void) { return fa::tls_last_kind; }
 int64_t fa_b200_launch_count(int reset) {
-  int64_t v = fa::tls_launches;
-  if (reset) fa::tls_launches = 0;
+  int64_t v = reset ? fa::g_launches.exchange(0) : fa::g_launches.load();
   return v;
 }
 

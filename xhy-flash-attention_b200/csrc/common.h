@@ -34,6 +34,8 @@ struct Error : public std::runtime_error {
 // per-thread bookkeeping (api.cu)
 void note_launch(int kind);  // kind: 1 generic SIMT, 2 tcgen05
 int device_sm_count();
+// optional per-kernel timing (fa_b200_profile_*): slot 0 = forward kernel, slot 1 = backward main kernel
+void profile_mark(int slot, bool begin, cudaStream_t s);
 int device_cc_major();
 
 // dispatchers (api.cu)

@@ -494,8 +494,9 @@ __global__ void __launch_bounds__(256) bwd_convert_dq_kernel(const Params p) {
 }
 
 void sanitize_b(TmaDesc4 &d) {
+  // a dimension of extent 1 never advances: give it a legal, monotonic stride
   for (int i = 1; i < 4; ++i)
-    if (d.dims[i] == 1) d.strides[i - 1] = 16;
+    if (d.dims[i] == 1) d.strides[i - 1] = (i == 1 ? d.dims[0] * 2 : d.strides[i - 2] * d.dims[i - 1] + 15) / 16 * 16;
 }
 TmaDesc4 bdesc(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch) {
   TmaDesc4 x;
@@ -550,7 +551,9 @@ template <int HD, bool kBf16> void launch_bwd(const Params &p, cudaStream_t s) {
       attr_set = true;
     }
     dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
+    profile_mark(1, true, s);
     kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm);
+    profile_mark(1, false, s);
     FA_CUDA(cudaGetLastError());
     note_launch(2);
   }

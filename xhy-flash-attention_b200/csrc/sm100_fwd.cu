@@ -404,8 +404,9 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
 
 void sanitize(TmaDesc4 &d) {
   // a dimension of extent 1 never advances: give it any legal (16-byte multiple) stride
+  // a dimension of extent 1 never advances: give it a legal, monotonic stride
   for (int i = 1; i < 4; ++i)
-    if (d.dims[i] == 1) d.strides[i - 1] = 16;
+    if (d.dims[i] == 1) d.strides[i - 1] = (i == 1 ? d.dims[0] * 2 : d.strides[i - 2] * d.dims[i - 1] + 15) / 16 * 16;
 }
 
 TmaDesc4 desc_for(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch, int box_rows) {
@@ -446,7 +447,9 @@ template <int HD, bool kBf16> void launch_fwd(const Params &p, cudaStream_t s) {
     attr_set = true;
   }
   const int grid = std::min(num_tiles, device_sm_count());
+  profile_mark(0, true, s);
   kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles);
+  profile_mark(0, false, s);
   FA_CUDA(cudaGetLastError());
   note_launch(2);
 }

@@ -26,6 +26,11 @@ static EncodeTiledFn encode_fn() {
 
 CUtensorMap make_tma_4d(const TmaDesc4 &d) {
   CUtensorMap m;
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {  // autograd worker threads start without a current driver context
+    FA_CUDA(cudaFree(nullptr));
+    ctx_bound = true;
+  }
   cuuint64_t dims[4] = {d.dims[0], d.dims[1], d.dims[2], d.dims[3]};
   cuuint64_t strides[3] = {d.strides[0], d.strides[1], d.strides[2]};
   cuuint32_t box[4] = {d.box[0], d.box[1], d.box[2], d.box[3]};
