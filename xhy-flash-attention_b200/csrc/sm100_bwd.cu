@@ -43,13 +43,14 @@ template <int HD> struct BwdSmem {
   static constexpr int kQ = kV + kTile;                  // 2 stages
   static constexpr int kDO = kQ + 2 * kTile;
   static constexpr int kDS = kDO + kTile;                // dS^T: 2 halves x (128 keys x 128 bytes)
-  static constexpr int kDQ = kDS + kB * kB * 2;          // dQ staging chunk: 128 rows x 32 floats
-  static constexpr int kVec = kDQ + kB * 32 * 4;         // [2 stages][lse2 | dpsum][128] floats
+  static constexpr int kDQ = kDS + kB * kB * 2;          // dQ staging: 2 chunks of 128 rows x 32 floats
+  static constexpr int kVec = kDQ + 2 * kB * 32 * 4;     // [2 stages][lse2 | dpsum][128] floats
   static constexpr int kBar = kVec + 2 * 2 * kB * 4;
   static constexpr int kNumBars = 16;
   static constexpr int kTmemSlot = kBar + kNumBars * 8;
   static constexpr int kTotal = kTmemSlot + 16;
-  static constexpr int kDynBytes = kTotal + 1024;
+  static constexpr int kDynBytes = kTotal;               // the dynamic smem base is 1024-byte aligned (checked at run time)
+  static_assert(kTotal <= 232448, "exceeds the 227 KB shared memory of an sm_100 CTA");
 };
 
 enum BwdBar {
@@ -122,9 +123,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t *smem = smem_raw;
   const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0) __trap();  // 128-byte swizzled tiles need a 1024-byte aligned base
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   auto bar = [&](int i) { return sbase + L::kBar + i * 8; };
   uint32_t *tmem_slot = (uint32_t *)(smem + L::kTmemSlot);
@@ -135,6 +137,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
   if (!live) return;  // uniform for the whole CTA
   const int nm = t.m_hi - t.m_lo;
   const int n_it = (t.hq1 - t.hq0) * nm;
+  const int n_it_u = __shfl_sync(0xffffffffu, n_it, 0);  // same value, provably warp-uniform for the issuer warp
 
   if (threadIdx.x == 0) {
     mbar_init(bar(BB_KV_FULL), 1);
@@ -161,7 +164,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
   const float scale_log2 = p.softmax_scale * kLog2e;
 
   if (warp >= 12) {
-    setmaxnreg_dec<96>();
+    setmaxnreg_dec<56>();
     if (warp == 13) {
       // ======================= producer =======================
       if (lane == 0 && n_it > 0) {
@@ -206,102 +209,119 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
         }
         __syncwarp();
       }
-    } else if (warp == 12 && lane == 0 && n_it > 0) {
+    } else if (warp == 12 && n_it_u > 0) {
       // ======================= MMA issuer =======================
+      // Whole warp, warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues.
+      const uint32_t tm = (uint32_t)__shfl_sync(0xffffffffu, (int)tmem, 0);
       constexpr uint32_t idesc_st = make_idesc(kBf16, kB, kB, false, false);   // S^T, dP^T: K-major x K-major
       constexpr uint32_t idesc_kv = make_idesc(kBf16, kB, HD, false, true);    // dV, dK: A in TMEM, B MN-major
       constexpr uint32_t idesc_dq = make_idesc(kBf16, kB, HD, true, true);     // dQ: A (dS^T) MN-major, B (K) MN-major
       const uint32_t sK = sbase + L::kK, sV = sbase + L::kV, sDO = sbase + L::kDO, sDS = sbase + L::kDS;
-      auto kmajor_pair = [&](uint32_t d_col, uint32_t a_base, uint32_t b_base) {
+      auto kmajor_pair = [&](uint32_t d_col, uint32_t a_base, uint32_t b_base, uint32_t done_bar) {
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k) {
-          const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
-          umma_ss(tmem + d_col, make_sdesc_sw128(a_base + off, 16, 1024), make_sdesc_sw128(b_base + off, 16, 1024),
-                  idesc_st, k > 0);
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
+            umma_ss(tm + d_col, make_sdesc_sw128(a_base + off, 16, 1024), make_sdesc_sw128(b_base + off, 16, 1024),
+                    idesc_st, k > 0);
+          }
+          umma_commit(done_bar);
         }
+        __syncwarp();
       };
-      auto tmem_a_mn_b = [&](uint32_t d_col, uint32_t a_col, uint32_t b_base, bool accumulate) {
+      auto tmem_a_mn_b = [&](uint32_t d_col, uint32_t a_col, uint32_t b_base, bool accumulate, uint32_t done_bar) {
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kB / 16; ++k) {
-          const uint32_t a = tmem + a_col + (k < 4 ? k * 8 : 64 + (k - 4) * 8);  // each compute warpgroup packs into its own half
-          umma_ts(tmem + d_col, a, make_sdesc_sw128(b_base + k * 2048, kHalfBytes, 1024), idesc_kv,
-                  (accumulate || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kB / 16; ++k) {
+            const uint32_t a = tm + a_col + (k < 4 ? k * 8 : 64 + (k - 4) * 8);  // each compute warpgroup packs into its own half
+            umma_ts(tm + d_col, a, make_sdesc_sw128(b_base + k * 2048, kHalfBytes, 1024), idesc_kv,
+                    (accumulate || k > 0) ? 1u : 0u);
+          }
+          umma_commit(done_bar);
         }
+        __syncwarp();
       };
       mbar_wait(bar(BB_KV_FULL), 0);
       mbar_wait(bar(BB_Q_FULL + 0), 0);
       tc_fence_after();
-      kmajor_pair(TS_, sK, sbase + L::kQ);
-      umma_commit(bar(BB_S_FULL));
-      for (int it = 0; it < n_it; ++it) {
+      kmajor_pair(TS_, sK, sbase + L::kQ, bar(BB_S_FULL));
+      for (int it = 0; it < n_it_u; ++it) {
         const int st = it & 1;
         const uint32_t sQ = sbase + L::kQ + st * L::kTile;
         mbar_wait(bar(BB_DO_FULL), it & 1);
         if (it > 0) mbar_wait(bar(BB_DQ_EMPTY), (it - 1) & 1);   // dQ(it-1) has left TMEM: the dP region is free
         tc_fence_after();
-        kmajor_pair(TDP, sV, sDO);
-        umma_commit(bar(BB_DP_FULL));
+        kmajor_pair(TDP, sV, sDO, bar(BB_DP_FULL));
         mbar_wait(bar(BB_P_FULL), it & 1);
         tc_fence_after();
-        tmem_a_mn_b(TDV, TS_, sDO, it > 0);
-        umma_commit(bar(BB_DO_EMPTY));
-        if (it + 1 < n_it) {
+        tmem_a_mn_b(TDV, TS_, sDO, it > 0, bar(BB_DO_EMPTY));
+        if (it + 1 < n_it_u) {
           mbar_wait(bar(BB_Q_FULL + (st ^ 1)), ((it + 1) >> 1) & 1);
           tc_fence_after();
-          kmajor_pair(TS_, sK, sbase + L::kQ + (st ^ 1) * L::kTile);
-          umma_commit(bar(BB_S_FULL));
+          kmajor_pair(TS_, sK, sbase + L::kQ + (st ^ 1) * L::kTile, bar(BB_S_FULL));
         }
         mbar_wait(bar(BB_DS_FULL), it & 1);
         tc_fence_after();
-        tmem_a_mn_b(TDK, TDP, sQ, it > 0);
-        umma_commit(bar(BB_Q_EMPTY + st));
+        tmem_a_mn_b(TDK, TDP, sQ, it > 0, bar(BB_Q_EMPTY + st));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kB / 16; ++k)
-          umma_ss(tmem + TDP, make_sdesc_sw128(sDS + k * 2048, kHalfBytes, 1024),
-                  make_sdesc_sw128(sK + k * 2048, kHalfBytes, 1024), idesc_dq, k > 0);
-        umma_commit(bar(BB_DQ_FULL));
+          for (int k = 0; k < kB / 16; ++k)
+            umma_ss(tm + TDP, make_sdesc_sw128(sDS + k * 2048, kHalfBytes, 1024),
+                    make_sdesc_sw128(sK + k * 2048, kHalfBytes, 1024), idesc_dq, k > 0);
+          umma_commit(bar(BB_DQ_FULL));
+        }
+        __syncwarp();
       }
-      umma_commit(bar(BB_DKV_FULL));
+      if (elect_one()) umma_commit(bar(BB_DKV_FULL));
+      __syncwarp();
     }
   } else if (warp >= 8) {
     // ======================= dQ reducers =======================
-    setmaxnreg_dec<120>();
+    // All of dQ (128 fp32 per row) is pulled out of TMEM first so that the dP/dS/dQ region is handed back to the MMA
+    // warp as early as possible; the smem staging + bulk reduce-add then runs off the critical path.
+    setmaxnreg_inc<184>();
     const int r = (warp % 4) * 32 + lane;
     const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
     const int tid = threadIdx.x - 256;
     const int n_chunks = p.d_rounded / 32 < HD / 32 ? p.d_rounded / 32 : HD / 32;
     uint8_t *stg = smem + L::kDQ;
+    uint32_t g = 0;  // bulk groups committed so far; group g uses staging buffer g & 1, last used by group g - 2
     for (int it = 0; it < n_it; ++it) {
       const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
       float *gtile = p.dq_accum + acc_tile_index(p, t, hq, m) * (int64_t)(p.d_rounded / 32) * (kB * 32);
       mbar_wait(bar(BB_DQ_FULL), it & 1);
       tc_fence_after();
-      for (int c = 0; c < n_chunks; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tmem + lane_base + TDP + c * 32, v);
-        tmem_wait_ld();
-        if (c == n_chunks - 1) {
-          tc_fence_before();
-          mbar_arrive(bar(BB_DQ_EMPTY));
-        }
-        if (tid == 0) bulk_wait_read<0>();          // the previous chunk has been read out of the staging buffer
-        named_bar_sync(3, 128);
+      uint32_t v[HD / 32][32];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4 *>(stg + r * 128 + ((j ^ (r & 7)) * 16)) =
-              make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        fence_proxy_async_smem();
-        named_bar_sync(4, 128);
-        if (tid == 0) {
-          bulk_reduce_add_f32(gtile + c * (kB * 32), smem_u32(stg), kB * 32 * 4);
-          bulk_commit();
+      for (int c = 0; c < HD / 32; ++c)
+        if (c < n_chunks) tmem_ld32(tmem + lane_base + TDP + c * 32, v[c]);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(bar(BB_DQ_EMPTY));
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        if (c < n_chunks) {
+          uint8_t *buf = stg + (g & 1) * (kB * 32 * 4);
+          if (tid == 0 && g >= 2) bulk_wait_read<1>();   // the group that last used this buffer has been read out
+          named_bar_sync(3, 128);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4 *>(buf + r * 128 + ((j ^ (r & 7)) * 16)) =
+                make_uint4(v[c][4 * j], v[c][4 * j + 1], v[c][4 * j + 2], v[c][4 * j + 3]);
+          fence_proxy_async_smem();
+          named_bar_sync(4, 128);
+          if (tid == 0) {
+            bulk_reduce_add_f32(gtile + c * (kB * 32), smem_u32(buf), kB * 32 * 4);
+            bulk_commit();
+          }
+          ++g;
         }
       }
     }
     if (tid == 0) bulk_wait<0>();
   } else {
     // ======================= compute warpgroups =======================
-    setmaxnreg_inc<144>();
+    setmaxnreg_inc<136>();
     const int wg = warp / 4;
     const int r = (warp % 4) * 32 + lane;          // key row inside the block == TMEM lane
     const int col = t.n0 + r;                      // key index

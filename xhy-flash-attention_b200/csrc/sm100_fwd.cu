@@ -27,7 +27,7 @@ constexpr int kBM = 128;          // rows per Q tile
 constexpr int kBN = 128;          // keys per K/V tile
 constexpr int kTilesPerCta = 2;   // Q tiles per work tile
 constexpr int kStages = 4;        // K/V ring depth
-constexpr int kThreads = 320;     // 2 softmax warpgroups + MMA warp + TMA warp
+constexpr int kThreads = 384;     // 2 softmax warpgroups + {MMA warp, TMA warp, 2 idle warps} (register-budget warpgroup)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 domain: P stays below 2^8
@@ -89,6 +89,17 @@ __device__ __forceinline__ bool decode_tile(const Params &p, int tile, int num_m
   return true;
 }
 
+// Broadcast the (data-dependent, e.g. cu_seqlens-derived) tile description from lane 0 so that the compiler can keep
+// loop bounds, stage indices and MMA descriptors in uniform registers in the single-issuer warps.
+__device__ __forceinline__ int bcast0(int v) { return __shfl_sync(0xffffffffu, v, 0); }
+__device__ __forceinline__ void uniformize(TileInfo &ti) {
+  ti.hq = bcast0(ti.hq); ti.hk = bcast0(ti.hk); ti.m0 = bcast0(ti.m0);
+  ti.q_row0 = bcast0(ti.q_row0); ti.k_row0 = bcast0(ti.k_row0); ti.q_b = bcast0(ti.q_b); ti.k_b = bcast0(ti.k_b);
+  ti.lo = bcast0(ti.lo); ti.hi = bcast0(ti.hi);
+#pragma unroll
+  for (int t = 0; t < 2; ++t) { ti.n_lo[t] = bcast0(ti.n_lo[t]); ti.n_hi[t] = bcast0(ti.n_hi[t]); }
+}
+
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -131,13 +142,18 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem_raw = *tmem_slot;
+  const uint32_t tmem = tmem_raw;
 
   constexpr int kHalves = HD / 64;            // 64-element (128-byte) boxes per row
   constexpr uint32_t kHalfBytes = kBM * 128;  // one box: 128 rows x 128 bytes
   const uint32_t scale_dummy = 0; (void)scale_dummy;
 
-  if (warp == 9) {
+  // register budget: 168 per thread at launch (384 threads); the issuer/producer warpgroup gives most of its registers
+  // to the two softmax warpgroups, which hold a full 128-column S row per thread
+  if (warp >= 8) {
+   asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+   if (warp == 9) {
     // ======================= TMA producer =======================
     if (lane == 0) {
       uint32_t kv_it = 0, qcnt[2] = {0, 0};
@@ -172,32 +188,46 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     }
   } else if (warp == 8) {
     // ======================= MMA issuer =======================
-    if (lane == 0) {
+    // The whole warp runs this (warp-uniform control flow keeps descriptors in uniform registers); one elected lane
+    // issues the tcgen05 instructions.
+    {
+      const uint32_t tmem = bcast0((int)tmem_raw);
       constexpr uint32_t idesc_s = make_idesc(kBf16, kBM, kBN, false, false);
       constexpr uint32_t idesc_o = make_idesc(kBf16, kBM, HD, false, true);
       uint32_t kv_it = 0, qcnt[2] = {0, 0}, pcnt[2] = {0, 0};
+      auto commit = [&](uint32_t b) {
+        if (elect_one()) umma_commit(b);
+        __syncwarp();
+      };
       auto issue_s = [&](int t, uint32_t kstage) {
         const uint32_t qa = sbase + L::kQOff + t * L::kTileBytes;
         const uint32_t ka = sbase + L::kKVOff + kstage * L::kTileBytes;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k) {
-          const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
-          umma_ss(tmem + t * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
-                  k > 0);
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k / 4) * kHalfBytes + (k % 4) * 32;
+            umma_ss(tmem + t * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
+                    k > 0);
+          }
+          umma_commit(bar(B_SFULL + t));
         }
-        umma_commit(bar(B_SFULL + t));
+        __syncwarp();
       };
       auto issue_pv = [&](int t, uint32_t vstage, bool accumulate) {
         const uint32_t va = sbase + L::kKVOff + vstage * L::kTileBytes;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kBN / 16; ++k)
-          umma_ts(tmem + 2 * kBN + t * HD, tmem + t * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kHalfBytes, 1024),
-                  idesc_o, (accumulate || k > 0) ? 1u : 0u);
-        umma_commit(bar(B_OFULL + t));
+          for (int k = 0; k < kBN / 16; ++k)
+            umma_ts(tmem + 2 * kBN + t * HD, tmem + t * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kHalfBytes, 1024),
+                    idesc_o, (accumulate || k > 0) ? 1u : 0u);
+          umma_commit(bar(B_OFULL + t));
+        }
+        __syncwarp();
       };
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         TileInfo ti;
-        if (!decode_tile(p, tile, num_m, ti)) continue;
+        if (!bcast0(decode_tile(p, tile, num_m, ti) ? 1 : 0)) continue;
+        uniformize(ti);
         if (ti.hi <= ti.lo) continue;
 #pragma unroll
         for (int t = 0; t < 2; ++t)
@@ -210,7 +240,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
 #pragma unroll
         for (int t = 0; t < 2; ++t)
           if (ti.lo >= ti.n_lo[t] && ti.lo < ti.n_hi[t]) issue_s(t, kst);
-        umma_commit(bar(B_KVEMPTY + kst));
+        commit(bar(B_KVEMPTY + kst));
         for (int j = ti.lo; j < ti.hi; ++j) {
           const uint32_t vst = kv_it % kStages;
           mbar_wait(bar(B_KVFULL + vst), (kv_it / kStages) & 1);
@@ -236,20 +266,22 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
               issue_s(t, nkst);
             }
           }
-          umma_commit(bar(B_KVEMPTY + vst));
+          commit(bar(B_KVEMPTY + vst));
           if (has_next) {
             if (!next_waited) {  // no tile uses block j+1 (cannot happen for the union range, kept for safety)
               nkst = kv_it % kStages;
               mbar_wait(bar(B_KVFULL + nkst), (kv_it / kStages) & 1);
             }
             ++kv_it;
-            umma_commit(bar(B_KVEMPTY + nkst));
+            commit(bar(B_KVEMPTY + nkst));
           }
         }
       }
     }
+   }
   } else {
     // ======================= softmax warpgroups =======================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     const int t = warp / 4;                    // Q tile of this warpgroup
     const int r_in_tile = threadIdx.x - t * kBM;
     const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
