@@ -125,6 +125,30 @@ __device__ __forceinline__ bool is_masked(const MaskCtx &m, int row, int col) {
   }
   return false;
 }
+// bit i (0 <= i < 32) is set iff position base + i lies OUTSIDE [lo, hi): the masked positions of a 32-wide chunk
+// when the visible set is an interval (seqlen tail, causal, sliding window).
+__device__ __forceinline__ uint32_t outside_bits(int lo, int hi, int base) {
+  lo = min(max(lo - base, 0), 32);
+  hi = min(max(hi - base, 0), 32);
+  if (hi <= lo) return 0xffffffffu;
+  const uint32_t below_hi = hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+  const uint32_t below_lo = (1u << lo) - 1u;  // lo < 32 here
+  return ~(below_hi & ~below_lo);
+}
+// visible key columns of a query row / visible query rows of a key column, as half-open intervals
+__device__ __forceinline__ void visible_cols(const MaskCtx &m, int row, int &lo, int &hi) {
+  lo = 0; hi = m.sk;
+  if (m.causal) hi = min(hi, row + (m.bottom_right ? m.shift : 0) + 1);
+  if (m.wr >= 0) hi = min(hi, row + m.shift + m.wr + 1);
+  if (m.wl >= 0) lo = max(lo, row + m.shift - m.wl);
+}
+__device__ __forceinline__ void visible_rows(const MaskCtx &m, int col, int &lo, int &hi) {
+  lo = 0; hi = 0x7fffffff;
+  if (col >= m.sk) { hi = 0; return; }
+  if (m.causal) lo = max(lo, col - (m.bottom_right ? m.shift : 0));
+  if (m.wr >= 0) lo = max(lo, col - m.shift - m.wr);
+  if (m.wl >= 0) hi = col - m.shift + m.wl + 1;
+}
 __device__ __forceinline__ MaskCtx make_mask_ctx(const Params &p, int bi, int head, int sq, int sk) {
   MaskCtx m;
   m.sq = sq; m.sk = sk; m.shift = sk - sq;

@@ -328,7 +328,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
     const uint32_t tS = tmem + lane_base + TS_ + wg * 64, tP = tmem + lane_base + TS_ + wg * 64;
     const uint32_t tDP = tmem + lane_base + TDP + wg * 64, tDS = tmem + lane_base + TDP + wg * 64;
-    uint8_t *ds_row = smem + L::kDS + wg * kHalfBytes + r * 128;
+    const uint32_t ds_row_a = sbase + L::kDS + wg * kHalfBytes + r * 128;
     const int shift = t.sk - t.sq;
     const int shiftc = p.causal_bottom_right ? shift : 0;
     for (int it = 0; it < n_it; ++it) {
@@ -339,8 +339,23 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
       const bool full = (t.n0 + kB <= t.sk) && (!mc.causal || t.n0 + kB - 1 <= m0 + shiftc) &&
                         (mc.wr < 0 || t.n0 + kB - 1 <= m0 + shift + mc.wr) &&
                         (mc.wl < 0 || t.n0 >= m0 + kB - 1 + shift - mc.wl) && (mc.lts == nullptr);
-      const float *lse2 = vec + (st * 2 + 0) * kB + wg * 64;
-      const float *dpsum = vec + (st * 2 + 1) * kB + wg * 64;
+      const uint32_t lse2_a = sbase + L::kVec + ((st * 2 + 0) * kB + wg * 64) * 4;
+      const uint32_t dpsum_a = sbase + L::kVec + ((st * 2 + 1) * kB + wg * 64) * 4;
+      // element mask of this thread's 64 (query, key) pairs: built in a rolled loop so that the generic mask rule is
+      // emitted once (boundary / flashmask blocks only); the hot loops below stay small enough for the instruction cache
+      uint32_t mbits[2] = {0u, 0u};
+      if (!full) {
+        if (mc.lts == nullptr) {  // seqlen tail / causal / window: the visible rows of a key column form an interval
+          int vlo, vhi;
+          visible_rows(mc, col, vlo, vhi);
+          mbits[0] = outside_bits(vlo, vhi, m0 + wg * 64);
+          mbits[1] = outside_bits(vlo, vhi, m0 + wg * 64 + 32);
+        } else {
+#pragma unroll 1
+          for (int i = 0; i < 64; ++i)
+            if (is_masked(mc, m0 + wg * 64 + i, col)) mbits[i >> 5] |= 1u << (i & 31);
+        }
+      }
       mbar_wait(bar(BB_Q_FULL + st), (it >> 1) & 1);   // LSE / dPsum rows of this query block are in smem
       mbar_wait(bar(BB_S_FULL), it & 1);
       tc_fence_after();
@@ -350,19 +365,23 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
         uint32_t s[32];
         tmem_ld32(tS + c2 * 32, s);
         tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const float4 l4 = lds128(lse2_a + (c2 * 32 + i) * 4);
+          pr[c2 * 32 + i + 0] = ex2f(fmaf(__uint_as_float(s[i + 0]), scale_log2, -l4.x));
+          pr[c2 * 32 + i + 1] = ex2f(fmaf(__uint_as_float(s[i + 1]), scale_log2, -l4.y));
+          pr[c2 * 32 + i + 2] = ex2f(fmaf(__uint_as_float(s[i + 2]), scale_log2, -l4.z));
+          pr[c2 * 32 + i + 3] = ex2f(fmaf(__uint_as_float(s[i + 3]), scale_log2, -l4.w));
+        }
+        if (!full) {
+          const uint32_t mb = mbits[c2];
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if ((mb >> i) & 1u) pr[c2 * 32 + i] = 0.f;
+        }
         uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const int qi = c2 * 32 + i;
-          float p0 = ex2f(fmaf(__uint_as_float(s[i]), scale_log2, -lse2[qi]));
-          float p1 = ex2f(fmaf(__uint_as_float(s[i + 1]), scale_log2, -lse2[qi + 1]));
-          if (!full) {
-            if (is_masked(mc, m0 + wg * 64 + qi, col)) p0 = 0.f;
-            if (is_masked(mc, m0 + wg * 64 + qi + 1, col)) p1 = 0.f;
-          }
-          pr[qi] = p0; pr[qi + 1] = p1;
-          pk[i / 2] = pack2<kBf16>(p0, p1);
-        }
+        for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[c2 * 32 + 2 * i], pr[c2 * 32 + 2 * i + 1]);
         tmem_st16(tP + c2 * 16, pk);
       }
       tmem_wait_st();
@@ -379,17 +398,19 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
         tmem_wait_ld();
         uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const int qi = c2 * 32 + i;
-          const float d0 = pr[qi] * (__uint_as_float(dp[i]) - dpsum[qi]);
-          const float d1 = pr[qi + 1] * (__uint_as_float(dp[i + 1]) - dpsum[qi + 1]);
-          pk[i / 2] = pack2<kBf16>(d0, d1);
+        for (int i = 0; i < 32; i += 4) {
+          const float4 d4 = lds128(dpsum_a + (c2 * 32 + i) * 4);
+          const float e0 = pr[c2 * 32 + i + 0] * (__uint_as_float(dp[i + 0]) - d4.x);
+          const float e1 = pr[c2 * 32 + i + 1] * (__uint_as_float(dp[i + 1]) - d4.y);
+          const float e2 = pr[c2 * 32 + i + 2] * (__uint_as_float(dp[i + 2]) - d4.z);
+          const float e3 = pr[c2 * 32 + i + 3] * (__uint_as_float(dp[i + 3]) - d4.w);
+          pk[i / 2] = pack2<kBf16>(e0, e1);
+          pk[i / 2 + 1] = pack2<kBf16>(e2, e3);
         }
         tmem_st16(tDS + c2 * 16, pk);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4 *>(ds_row + (((c2 * 4 + j) ^ (r & 7)) * 16)) =
-              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          sts128(ds_row_a + (((c2 * 4 + j) ^ (r & 7)) * 16), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
       }
       tmem_wait_st();
       tc_fence_before();

@@ -325,11 +325,26 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
                           (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
                           (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) && (mc.lts == nullptr);
         if (!full) {
+          // boundary / flashmask blocks: the generic mask rule runs in a rolled loop (emitted once, keeps the hot loop
+          // inside the instruction cache); the unrolled pass below only applies the resulting bit mask
+          uint32_t mb[4];
+          if (mc.lts == nullptr) {  // seqlen tail / causal / window: the visible columns of a row form an interval
+            int vlo, vhi;
+            visible_cols(mc, row, vlo, vhi);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) mb[c] = outside_bits(vlo, vhi, c0 + c * 32);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) mb[c] = 0u;
+#pragma unroll 1
+            for (int i = 0; i < kBN; ++i)
+              if (is_masked(mc, row, c0 + i)) mb[i >> 5] |= 1u << (i & 31);
+          }
 #pragma unroll
           for (int c = 0; c < 4; ++c)
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              if (is_masked(mc, row, c0 + c * 32 + i)) s[c][i] = __float_as_uint(-CUDART_INF_F);
+              if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
         }
         float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
 #pragma unroll
