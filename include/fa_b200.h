@@ -98,6 +98,11 @@ bool fa_b200_fwd_combine(const fa_b200_params *p, cudaStream_t stream);
 /* Split heuristic.  Equivalent of fa3_get_num_splits (csrc/flashmask_v2/heuristics.h:22-59). */
 int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seqlen_k, int head_size, int num_sm);
 
+/* Split count for the TMA-fed decode kernel of this library (decode.cu): two CTAs are resident per SM, a CTA streams
+ * 128-key blocks; picks the split count that minimises waves x (blocks per split + fixed per-CTA cost).  The reference
+ * heuristic above is kept for callers that want its exact answer; this one is what flash_attn_with_kvcache uses. */
+int fa_b200_decode_num_splits(int batch, int num_heads_k, int seqlen_k, int num_sm);
+
 /* Append new K/V rows into the cache at position seqused_k[b] (flash_attn_with_kvcache's k=/v= arguments;
  * reference: csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1542 store_kv_new). */
 bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache,
@@ -124,7 +129,7 @@ float fa_b200_profile_last_ms(int slot);
 
 /* Introspection for tests/bench. */
 int fa_b200_abi_version(void);
-/* which kernel family served the last call on this thread: 0 none, 1 generic SIMT, 2 tcgen05 */
+/* which kernel family served the last call on this thread: 0 none, 1 generic SIMT, 2 tcgen05, 3 TMA-fed decode */
 int fa_b200_last_kernel_kind(void);
 /* number of kernels launched by this library (all threads) since the last reset */
 int64_t fa_b200_launch_count(int reset);

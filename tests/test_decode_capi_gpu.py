@@ -188,3 +188,62 @@ def test_lse_merge(capi):
     torch.testing.assert_close(acc, exp, atol=2e-2, rtol=2e-2)
     exp_l = lse_full[0].t().clone(); exp_l[5] = l2[5]
     torch.testing.assert_close(l1, exp_l, atol=1e-4, rtol=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("h,hk,sq", [(32, 8, 1), (16, 2, 2), (8, 8, 3), (16, 1, 1), (32, 2, 1)])
+@pytest.mark.parametrize("num_splits", [0, 1, 5])
+def test_decode_kernel_shapes(fa, capi, h, hk, sq, num_splits, dtype):
+    """The TMA-fed decode kernel (csrc/decode.cu): pack-GQA group sizes 1..16, NaN garbage beyond cache_seqlens,
+    lengths that are not multiples of the 64-key tile; h=32/hk=2 (group 16, sq 1) fills all 16 packed rows."""
+    torch.manual_seed(1)
+    b, sk, d = 4, 2111, 128
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=dtype)
+    kc = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype)
+    vc = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype)
+    seqlens = torch.tensor([2111, 1, 64, 1000], device=DEV, dtype=torch.int32)
+    for i in range(b):  # rows beyond the used length hold NaN: they must not leak into the result
+        kc[i, int(seqlens[i]):] = float("nan")
+        vc[i, int(seqlens[i]):] = float("nan")
+    out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=seqlens, causal=True, num_splits=num_splits,
+                                          return_softmax_lse=True)
+    assert capi.last_kernel_kind() in (1, 3)
+    (ref, pt), lse_ref = _kvcache_ref(q, kc, vc, seqlens, True)
+    check_2x("out", out, ref, pt)
+    check_lse(lse, lse_ref)
+
+
+def test_decode_kernel_is_used(fa, capi):
+    torch.manual_seed(0)
+    q = torch.randn(2, 1, 32, 128, device=DEV, dtype=torch.bfloat16)
+    kc = torch.randn(2, 4096, 8, 128, device=DEV, dtype=torch.bfloat16)
+    vc = torch.randn(2, 4096, 8, 128, device=DEV, dtype=torch.bfloat16)
+    capi.launch_count(reset=True)
+    fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=4096, causal=True, num_splits=1)
+    assert capi.launch_count() == 1
+    # the split launch is recorded as kind 3 (TMA-fed decode kernel); the combine kernel follows it
+    lib = capi.load()
+    p_kind = []
+    fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=4096, causal=True, num_splits=1)
+    p_kind.append(capi.last_kernel_kind())
+    assert p_kind == [3]
+    # more than 16 packed rows: outside the decode kernel's envelope, served by the generic kernel
+    q2 = torch.randn(2, 5, 32, 128, device=DEV, dtype=torch.bfloat16)
+    fa.flash_attn_with_kvcache(q2, kc, vc, cache_seqlens=4096, causal=True, num_splits=1)
+    assert capi.last_kernel_kind() == 1
+
+
+@pytest.mark.parametrize("window", [(128, 0), (300, -1), (-1, 0)])
+@pytest.mark.parametrize("sq", [1, 4])
+def test_decode_window(fa, window, sq):
+    torch.manual_seed(2)
+    b, sk, h, hk, d = 2, 1111, 8, 2, 64
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16)
+    kc = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16)
+    vc = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16)
+    seqlens = torch.tensor([1111, 500], device=DEV, dtype=torch.int32)
+    out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=seqlens, window_size=window, num_splits=3,
+                                          return_softmax_lse=True)
+    (ref, pt), lse_ref = _kvcache_ref(q, kc, vc, seqlens, False, window)
+    check_2x("out", out, ref, pt)
+    check_lse(lse, lse_ref)

@@ -69,6 +69,8 @@ def load() -> C.CDLL:
     lib.fa_b200_flashmask_prepare.restype = C.c_bool
     lib.fa_b200_num_splits.argtypes = [C.c_int] * 6
     lib.fa_b200_num_splits.restype = C.c_int
+    lib.fa_b200_decode_num_splits.argtypes = [C.c_int] * 4
+    lib.fa_b200_decode_num_splits.restype = C.c_int
     lib.fa_b200_append_kv.argtypes = ([C.c_void_p] * 5 + [C.c_int] * 6 + [C.c_int64] * 6 + [C.c_void_p])
     lib.fa_b200_append_kv.restype = C.c_bool
     lib.fa_b200_lse_merge.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int,

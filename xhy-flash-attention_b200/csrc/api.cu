@@ -195,6 +195,25 @@ int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seql
   return 1;
 }
 
+int fa_b200_decode_num_splits(int batch, int num_heads_k, int seqlen_k, int num_sm) {
+  if (num_sm <= 0) num_sm = 148;
+  const int slots = 2 * num_sm;               // decode_kernel: 2 resident CTAs per SM
+  const int base = batch * num_heads_k;
+  const int nblk = (seqlen_k + 127) / 128;
+  const int overhead = 2;                     // per-CTA prologue + merge, in units of one 128-key block
+  int best_s = 1;
+  long best_cost = -1;
+  const int max_s = nblk < 64 ? nblk : 64;
+  for (int s = 1; s <= max_s; ++s) {
+    const int per = (nblk + s - 1) / s;
+    if (s > 1 && per < 2) break;
+    const long waves = ((long)base * s + slots - 1) / slots;
+    const long cost = waves * (per + overhead);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_s = s; }
+  }
+  return best_s;
+}
+
 bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache,
                        const int32_t *cache_seqlens, int batch, int seqlen_new, int seqlen_cache,
                        int num_heads_k, int head_size, int is_bf16,

@@ -443,7 +443,8 @@ def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None
     q: (batch, seqlen_q, nheads, headdim); k_cache, v_cache: (batch, seqlen_cache, nheads_k, headdim).
     If ``k``/``v`` are given they are appended IN PLACE at ``cache_seqlens`` before attention.  ``causal`` and
     ``window_size`` are bottom-right aligned (csrc/flashmask_v2/mask.h:85-118).  ``num_splits=0`` picks the split
-    count with the reference heuristic (csrc/flashmask_v2/heuristics.h:22-59); partial results are merged by the
+    count (decode shapes: the wave model of ``fa_b200_decode_num_splits``; otherwise the reference heuristic,
+    csrc/flashmask_v2/heuristics.h:22-59); partial results are merged by the
     LSE-combine kernel.  Inference only (no autograd).
     """
     for name, val in (("rotary_cos", rotary_cos), ("rotary_sin", rotary_sin), ("cache_batch_idx", cache_batch_idx),
@@ -494,7 +495,10 @@ def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None
             p.seqused_k = seqused.data_ptr()
         if num_splits <= 0:
             num_sm = torch.cuda.get_device_properties(q.device).multi_processor_count
-            num_splits = lib.fa_b200_num_splits(b, h_k, sq * (h // h_k), sk, d, num_sm)
+            if sq * (h // h_k) <= 16 and d in (64, 128):   # the TMA-fed decode kernel (csrc/decode.cu)
+                num_splits = lib.fa_b200_decode_num_splits(b, h_k, sk, num_sm)
+            else:
+                num_splits = lib.fa_b200_num_splits(b, h_k, sq * (h // h_k), sk, d, num_sm)
         p.num_splits = num_splits
         if num_splits > 1:
             oaccum = torch.empty((num_splits, b, sq, h, d), dtype=torch.float32, device=q.device)
