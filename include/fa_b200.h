@@ -117,10 +117,12 @@ bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void
 bool fa_b200_flashmask_prepare(const fa_b200_params *p, int block_n, cudaStream_t stream);
 
 /* ring-attention step merge: (o, lse) <- merge((o, lse), (o_step, lse_step)) elementwise by LSE.
- * o (rows, h, d) bf16/fp16 or fp32 per o_is_fp32; lse (h, rows)-agnostic: lse index = row * lse_row_stride + head * lse_head_stride. */
+ * o (rows, h, d) bf16/fp16 or fp32 per o_is_fp32; lse / lse_step layouts are free: index = row * row_stride + head * head_stride
+ * (the running lse is kept (rows, h); a kernel's own lse is (h, rows)).  +inf and -inf both mean "no contribution". */
 bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse_step,
                        int64_t rows, int heads, int head_size, int is_bf16, int o_is_fp32,
-                       int64_t lse_row_stride, int64_t lse_head_stride, cudaStream_t stream);
+                       int64_t lse_row_stride, int64_t lse_head_stride,
+                       int64_t lse_step_row_stride, int64_t lse_step_head_stride, cudaStream_t stream);
 
 /* Per-kernel device timing for bench.py's roofline (CUDA events recorded on the launch stream around the
  * dominant kernels).  slot 0 = forward kernel, slot 1 = backward main kernel.  Process-wide; not for concurrent use. */

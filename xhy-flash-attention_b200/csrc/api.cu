@@ -236,11 +236,11 @@ bool fa_b200_flashmask_prepare(const fa_b200_params *p, int block_n, cudaStream_
 
 bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads,
                        int head_size, int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride,
-                       cudaStream_t stream) {
+                       int64_t lse_step_row_stride, int64_t lse_step_head_stride, cudaStream_t stream) {
   FA_BEGIN
   FA_CHECK(o && lse && o_step && lse_step, "lse_merge: null tensor");
   fa::lse_merge(o, lse, o_step, lse_step, rows, heads, head_size, is_bf16, o_is_fp32, lse_row_stride,
-                lse_head_stride, stream);
+                lse_head_stride, lse_step_row_stride, lse_step_head_stride, stream);
   FA_END
 }
 

@@ -133,14 +133,14 @@ append_kv_kernel(const uint4 *k_new, const uint4 *v_new, uint4 *k_cache, uint4 *
 template <typename TO, typename TS>
 __global__ void __launch_bounds__(128)
 lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int64_t rows, int heads, int d,
-                 int64_t lrs, int64_t lhs) {
+                 int64_t lrs, int64_t lhs, int64_t srs, int64_t shs) {
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int64_t item = (int64_t)blockIdx.x * 4 + warp;
   if (item >= rows * heads) return;
   const int hh = item % heads;
   const int64_t row = item / heads;
   const int64_t li = row * lrs + hh * lhs;
-  const float l1 = lse[li], l2 = lse_step[li];
+  const float l1 = lse[li], l2 = lse_step[row * srs + hh * shs];
   const bool e1 = isinf(l1), e2 = isinf(l2);
   if (e2) return;  // nothing to add
   float w1, w2, ln;
@@ -199,14 +199,14 @@ void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cach
 }
 
 void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
-               int is_bf16, int o_is_fp32, int64_t lrs, int64_t lhs, cudaStream_t s) {
+               int is_bf16, int o_is_fp32, int64_t lrs, int64_t lhs, int64_t srs, int64_t shs, cudaStream_t s) {
   dim3 grid((unsigned)((rows * heads + 3) / 4));
   if (o_is_fp32) {
-    if (is_bf16) lse_merge_kernel<float, __nv_bfloat16><<<grid, 128, 0, s>>>((float *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs);
-    else lse_merge_kernel<float, __half><<<grid, 128, 0, s>>>((float *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs);
+    if (is_bf16) lse_merge_kernel<float, __nv_bfloat16><<<grid, 128, 0, s>>>((float *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
+    else lse_merge_kernel<float, __half><<<grid, 128, 0, s>>>((float *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
   } else {
-    if (is_bf16) lse_merge_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 128, 0, s>>>((__nv_bfloat16 *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs);
-    else lse_merge_kernel<__half, __half><<<grid, 128, 0, s>>>((__half *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs);
+    if (is_bf16) lse_merge_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 128, 0, s>>>((__nv_bfloat16 *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
+    else lse_merge_kernel<__half, __half><<<grid, 128, 0, s>>>((__half *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
   }
   FA_CUDA(cudaGetLastError());
   note_launch(1);

@@ -64,7 +64,8 @@ void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cach
                int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16,
                int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s);
 void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
-               int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride, cudaStream_t s);
+               int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride, int64_t step_row_stride,
+               int64_t step_head_stride, cudaStream_t s);
 
 // ---- device helpers shared by every kernel ------------------------------------------------------
 struct SeqInfo {
