@@ -226,6 +226,43 @@ def combine_ref(o_partial: torch.Tensor, lse_partial: torch.Tensor):
     return o, lse
 
 
+def merge_ref(o_acc, lse_acc, o_step, lse_step):
+    """Two-way LSE merge used by ring attention (same algebra as ``combine_ref``); an infinite LSE of either sign
+    means "no contribution".  o (..., d) fp32, lse (...) fp32.  Returns (o, lse)."""
+    e1, e2 = torch.isinf(lse_acc), torch.isinf(lse_step)
+    l1 = torch.where(e1, torch.full_like(lse_acc, NEG_INF), lse_acc)
+    l2 = torch.where(e2, torch.full_like(lse_step, NEG_INF), lse_step)
+    o, lse = combine_ref(torch.stack([o_acc.float(), o_step.float()]), torch.stack([l1, l2]))
+    both = e1 & e2
+    return o, torch.where(both, lse_acc, lse)
+
+
+def attention_block_bwd_ref(dout, q, k, v, out, lse, mask=None, softmax_scale=None):
+    """Backward of ONE (query block, key block) pair given the FINAL out / lse of the whole row
+    (csrc/flash_attn/src/flash_bwd_kernel.h:847 ``P = exp(S - LSE)``, :112-188 ``dPsum = rowsum(dO o O)``,
+    :897-906 ``dS = P o (dP - dPsum)``).  fp32.  q, dout, out (b, sq, h, d); k, v (b, sk, h_k, d); lse (b, h, sq).
+    Returns (dq, dk, dv) fp32 with dk/dv summed over the q-heads of each kv-head."""
+    b, sq, h, d = q.shape
+    hk = k.shape[2]
+    g = h // hk
+    qf, kf, vf, of, gf = q.float(), k.float().repeat_interleave(g, 2), v.float().repeat_interleave(g, 2), out.float(), dout.float()
+    scale = (1.0 / math.sqrt(d)) if softmax_scale is None else softmax_scale
+    s = torch.einsum("bthd,bshd->bhts", qf, kf) * scale
+    if mask is not None:
+        s = s.masked_fill(mask.to(s.device), NEG_INF)
+    lse_ = torch.where(torch.isinf(lse), torch.full_like(lse, float("inf")), lse)
+    p = torch.exp(s - lse_.unsqueeze(-1))
+    dp = torch.einsum("bthd,bshd->bhts", gf, vf)
+    dpsum = (gf * of).sum(-1).permute(0, 2, 1)                      # (b, h, sq)
+    ds = p * (dp - dpsum.unsqueeze(-1))
+    dq = torch.einsum("bhts,bshd->bthd", ds, kf) * scale
+    dk = torch.einsum("bhts,bthd->bshd", ds, qf) * scale
+    dv = torch.einsum("bhts,bthd->bshd", p, gf)
+    dk = dk.view(b, -1, hk, g, d).sum(3)
+    dv = dv.view(b, -1, hk, g, d).sum(3)
+    return dq, dk, dv
+
+
 # --------------------------------------------------------------------------- #
 # FLOP convention (benchmarks/benchmark_flash_attention.py:27-30)             #
 # --------------------------------------------------------------------------- #

@@ -182,7 +182,7 @@ def test_lse_merge(capi):
     acc = o1[0].clone().contiguous()
     step = o2[0].to(torch.bfloat16).contiguous()
     assert lib.fa_b200_lse_merge(acc.data_ptr(), l1.data_ptr(), step.data_ptr(), l2.data_ptr(), rows, h, d, 1, 1,
-                                 h, 1, torch.cuda.current_stream().cuda_stream), capi.last_error()
+                                 h, 1, h, 1, torch.cuda.current_stream().cuda_stream), capi.last_error()
     torch.cuda.synchronize()
     exp = full[0].clone(); exp[5] = o2[0, 5]
     torch.testing.assert_close(acc, exp, atol=2e-2, rtol=2e-2)

@@ -117,6 +117,14 @@ class _Rotation:
         self.recv = [torch.empty_like(t) for t in tensors]
         self.stream = comm_stream
         self.keep = tensors
+        self.staged = None
+        if tensors and tensors[0].is_cuda and dist.get_backend(group) == "gloo":
+            # debug transport for boxes with fewer GPUs than ranks (several ranks share one device, which NCCL refuses):
+            # the blocks go through host memory.  Never taken with the nccl backend.
+            self.staged = self.recv
+            tensors = [t.cpu() for t in tensors]
+            self.recv = [torch.empty_like(t) for t in tensors]
+            self.stream = comm_stream = None
         ops = []
         for t, r in zip(tensors, self.recv):
             ops.append(dist.P2POp(dist.isend, t, nxt, group))
@@ -131,6 +139,10 @@ class _Rotation:
     def wait(self):
         for r in self.reqs:
             r.wait()
+        if self.staged is not None:
+            for dst, src in zip(self.staged, self.recv):
+                dst.copy_(src)
+            return self.staged
         if self.stream is not None:
             torch.cuda.current_stream().wait_stream(self.stream)
             for t in self.keep + self.recv:
