@@ -150,3 +150,68 @@ def test_local_window(fa, sq, sk, window, generic):
     check_2x("dq", dq, *ref["dq"])
     check_2x("dk", dk, *ref["dk"])
     check_2x("dv", dv, *ref["dv"])
+
+
+def _big_flashmask(kind, b, hm, s, gen):
+    """Masks whose masked regions cover whole 128x128 blocks, so that block skipping in the tcgen05 kernels is exercised
+    (fully masked blocks dropped, partially masked blocks take the element rule, clear blocks take neither)."""
+    if kind == "doc_causal":
+        outs = []
+        for _ in range(b * hm):
+            cuts = sorted(torch.randint(1, s, (4,), generator=gen).tolist())
+            lens = [cuts[0]] + [cuts[i + 1] - cuts[i] for i in range(3)] + [s - cuts[3]]
+            outs.append(orc.document_lt_start([n for n in lens if n > 0]))
+        return (torch.stack(outs).view(b, hm, s).int(), None, None, None), True
+    if kind == "bidir_doc":
+        cuts = [0, s // 5, s // 2 + 37, s]
+        ends = torch.cat([torch.full((cuts[i + 1] - cuts[i],), cuts[i + 1]) for i in range(3)])
+        starts = torch.cat([torch.full((cuts[i + 1] - cuts[i],), cuts[i]) for i in range(3)])
+        e = ends.view(1, 1, s).expand(b, hm, s).int().clone()
+        st = starts.view(1, 1, s).expand(b, hm, s).int().clone()
+        return (e, None, None, st), False
+    if kind == "sliding_in_doc":   # causal, rows [j + w, end of doc) visible again is NOT expressible; band = [lts, lte)
+        j = torch.arange(s).view(1, 1, s)
+        w = 200
+        lts = (j + w).clamp(max=s).expand(b, hm, s).int().clone()          # rows >= j + w masked ...
+        lte = torch.full((b, hm, s), s, dtype=torch.int32)                 # ... to the end: causal sliding window
+        return (lts, lte, None, None), True
+    if kind == "four_blocks":      # two wide bands per column, piecewise constant over 96-column groups
+        grp = (torch.arange(s) // 96).view(1, 1, s)
+        ngrp = int(grp.max()) + 1
+        base = torch.randint(s // 2, s, (b, hm, ngrp), generator=gen)
+        lts = torch.gather(base, 2, grp.expand(b, hm, s))
+        lte = torch.minimum(lts + 300, torch.tensor(s))
+        ub = torch.randint(0, s // 4, (b, hm, ngrp), generator=gen)
+        uts = torch.gather(ub, 2, grp.expand(b, hm, s))
+        ute = torch.minimum(uts + 280, lts)
+        return (lts.int(), lte.int(), uts.int(), ute.int()), False
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("kind", ["doc_causal", "bidir_doc", "sliding_in_doc", "four_blocks"])
+@pytest.mark.parametrize("s,h,hk,hm", [(1536, 4, 2, 1), (1100, 4, 4, 4), (2048, 8, 2, 2)])
+def test_flashmask_block_skipping(fa, capi, kind, s, h, hk, hm):
+    gen = torch.Generator().manual_seed(3)
+    torch.manual_seed(3)
+    b, d = 2, 128
+    vecs, causal = _big_flashmask(kind, b, hm, s, gen)
+    q = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16)
+    dvecs = tuple(None if x is None else x.to(DEV) for x in vecs)
+    out, lse, _ = fa.flash_attn_func(q, k, v, 0.0, None, causal, True, flashmask=dvecs)
+    assert capi.last_kernel_kind() == 2
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    dense = orc.flashmask_dense(s, s, *vecs).repeat_interleave(h // hm, dim=1)
+    if causal:
+        dense = dense | orc.causal_mask_top_left(s, s)
+    ref = oracle_all(q.detach(), k.detach(), v.detach(), g, dense.to(DEV))
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dk, *ref["dk"])
+    check_2x("dv", dv, *ref["dv"])
+    # the generic SIMT kernels (no block skipping) must agree with the tcgen05 kernels
+    out_g = fa.flash_attn_func(q, k, v, 0.0, None, causal, flashmask=dvecs, _force_generic=True)
+    torch.testing.assert_close(out.float(), out_g.float(), atol=2e-2, rtol=2e-2)

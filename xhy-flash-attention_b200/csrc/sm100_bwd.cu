@@ -118,7 +118,70 @@ __device__ __forceinline__ int64_t acc_tile_index(const Params &p, const BwdTile
   return (int64_t)t.acc_tile0 + (int64_t)hq * t.acc_tiles_per_head + m;
 }
 
-template <int HD, bool kBf16>
+// The (q-head, query block) pairs one CTA visits, in the order every role walks them.  Per q-head the query blocks
+// are [m_lo, m_hi) minus the blocks that FlashMask covers completely for ALL keys of this CTA's key block: rows
+// [lts_max, lte_min) and [uts_max, ute_min) (per-block min/max of the mask vectors, flashmask_scan_kernel) -- at most
+// three surviving ranges, the same cut the reference makes (mainloop_bwd_sm90_tma_gmma_ws.hpp:1249-1299).
+template <bool kFM> struct MCursor {
+  int hq, hq1, ri, m, end, s0, e0, s1, e1, s2, e2;   // scalars: no dynamically indexed arrays (local memory)
+  int v[8];   // lts_max, lts_min, ute_max, ute_min, lte_max, lte_min, uts_max, uts_min of (mask head, key block)
+  bool has_ute;
+
+  __device__ __forceinline__ void load_head(const Params &p, const BwdTile &t, int h) {
+    s0 = t.m_lo; e0 = t.m_hi; s1 = e1 = s2 = e2 = 0;
+    if constexpr (kFM) {
+      const int nbp = (ceil_div(p.seqlen_k, kB) + 3) & ~3;
+      const int64_t plane = (int64_t)p.b * p.h_mask * nbp;
+      const int32_t *mm = p.flashmask_maxmin + ((int64_t)t.bi * p.h_mask + h / (p.h / p.h_mask)) * nbp + t.n0 / kB;
+      has_ute = p.ut_end != nullptr;
+      v[0] = mm[0]; v[1] = mm[plane];
+      v[2] = has_ute ? mm[2 * plane] : 0; v[3] = has_ute ? mm[3 * plane] : 0;
+      v[4] = p.lt_end ? mm[4 * plane] : 0x7fffffff; v[5] = p.lt_end ? mm[5 * plane] : 0x7fffffff;
+      v[6] = p.ut_start ? mm[6 * plane] : 0; v[7] = p.ut_start ? mm[7 * plane] : 0;
+      // fully masked block intervals [a0, a1) (lower-triangle band) and [b0, b1) (upper-triangle band), clipped
+      int a0 = min(max((int)(((int64_t)v[0] + kB - 1) / kB), t.m_lo), t.m_hi);
+      int a1 = v[5] >= t.sq ? t.m_hi : min(max(v[5] / kB, t.m_lo), t.m_hi);
+      int b0 = t.m_hi, b1 = t.m_hi;
+      if (has_ute) {
+        b0 = min(max((v[6] + kB - 1) / kB, t.m_lo), t.m_hi);
+        b1 = v[3] >= t.sq ? t.m_hi : min(max(v[3] / kB, t.m_lo), t.m_hi);
+      }
+      if (a1 < a0) a1 = a0;
+      if (b1 < b0) b1 = b0;
+      if (b0 < a0) { int x = a0; a0 = b0; b0 = x; x = a1; a1 = b1; b1 = x; }   // order by start
+      s0 = t.m_lo; e0 = a0;
+      s1 = a1; e1 = max(b0, a1);
+      s2 = max(b1, a1); e2 = t.m_hi;
+    }
+  }
+  __device__ __forceinline__ int count() const {
+    return max(e0 - s0, 0) + max(e1 - s1, 0) + max(e2 - s2, 0);
+  }
+  __device__ __forceinline__ void init(const BwdTile &t) { hq = t.hq0 - 1; hq1 = t.hq1; ri = 2; m = 0; end = 0; }
+  __device__ __forceinline__ bool next(const Params &p, const BwdTile &t) {
+    ++m;
+    while (true) {
+      if (m < end) return true;
+      ++ri;
+      if (ri == 1) { m = s1; end = e1; }
+      else if (ri == 2) { m = s2; end = e2; }
+      else {
+        if (++hq >= hq1) return false;
+        load_head(p, t, hq);
+        ri = 0; m = s0; end = e0;
+      }
+    }
+  }
+  // may FlashMask mask single elements of query block m (for this key block)?
+  __device__ __forceinline__ bool partial(const BwdTile &t) const {
+    if constexpr (!kFM) return false;
+    const int r0 = m * kB, r1 = min(r0 + kB, t.sq);
+    const bool clear = (r1 <= v[1] || r0 >= v[4]) && (!has_ute || r1 <= v[7] || r0 >= v[2]);
+    return !clear;
+  }
+};
+
+template <int HD, bool kBf16, bool kFM>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) {
   using L = BwdSmem<HD>;
@@ -135,8 +198,11 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
   BwdTile t;
   const bool live = bwd_decode(p, t);
   if (!live) return;  // uniform for the whole CTA
-  const int nm = t.m_hi - t.m_lo;
-  const int n_it = (t.hq1 - t.hq0) * nm;
+  int n_it = 0;
+  {
+    MCursor<kFM> c;
+    for (int h = t.hq0; h < t.hq1; ++h) { c.load_head(p, t, h); n_it += c.count(); }
+  }
   const int n_it_u = __shfl_sync(0xffffffffu, n_it, 0);  // same value, provably warp-uniform for the issuer warp
 
   if (threadIdx.x == 0) {
@@ -175,9 +241,11 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
           tma_load_4d(sbase + L::kV + hf * kHalfBytes, &tm.v, bar(BB_KV_FULL), hf * 64, t.hk, t.k_row0 + t.n0, t.k_b);
         }
       }
-      for (int it = 0; it < n_it; ++it) {
+      MCursor<kFM> cur;
+      cur.init(t);
+      for (int it = 0; cur.next(p, t); ++it) {
         const int st = it & 1;
-        const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+        const int hq = cur.hq, m = cur.m;
         mbar_wait(bar(BB_Q_EMPTY + st), ((it >> 1) & 1) ^ 1);
         const float *lse = p.softmax_lse + ((int64_t)t.bi * p.h + hq) * p.seqlen_q;
         const float *dps = p.softmax_d + ((int64_t)t.bi * p.h + hq) * p.seqlen_q_rounded;
@@ -286,8 +354,10 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     const int n_chunks = p.d_rounded / 32 < HD / 32 ? p.d_rounded / 32 : HD / 32;
     uint8_t *stg = smem + L::kDQ;
     uint32_t g = 0;  // bulk groups committed so far; group g uses staging buffer g & 1, last used by group g - 2
-    for (int it = 0; it < n_it; ++it) {
-      const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+    MCursor<kFM> cur;
+    cur.init(t);
+    for (int it = 0; cur.next(p, t); ++it) {
+      const int hq = cur.hq, m = cur.m;
       float *gtile = p.dq_accum + acc_tile_index(p, t, hq, m) * (int64_t)(p.d_rounded / 32) * (kB * 32);
       mbar_wait(bar(BB_DQ_FULL), it & 1);
       tc_fence_after();
@@ -331,21 +401,25 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     const uint32_t ds_row_a = sbase + L::kDS + wg * kHalfBytes + r * 128;
     const int shift = t.sk - t.sq;
     const int shiftc = p.causal_bottom_right ? shift : 0;
-    for (int it = 0; it < n_it; ++it) {
+    MCursor<kFM> cur;
+    cur.init(t);
+    for (int it = 0; cur.next(p, t); ++it) {
       const int st = it & 1;
-      const int hq = t.hq0 + it / nm, m = t.m_lo + it % nm;
+      const int hq = cur.hq, m = cur.m;
       const int m0 = m * kB;
+      const bool fm_partial = cur.partial(t);
       const MaskCtx mc = make_mask_ctx(p, t.bi, hq, t.sq, t.sk);
       const bool full = (t.n0 + kB <= t.sk) && (!mc.causal || t.n0 + kB - 1 <= m0 + shiftc) &&
                         (mc.wr < 0 || t.n0 + kB - 1 <= m0 + shift + mc.wr) &&
-                        (mc.wl < 0 || t.n0 >= m0 + kB - 1 + shift - mc.wl) && (mc.lts == nullptr);
+                        (mc.wl < 0 || t.n0 >= m0 + kB - 1 + shift - mc.wl) &&
+                        (kFM ? !fm_partial : (mc.lts == nullptr));
       const uint32_t lse2_a = sbase + L::kVec + ((st * 2 + 0) * kB + wg * 64) * 4;
       const uint32_t dpsum_a = sbase + L::kVec + ((st * 2 + 1) * kB + wg * 64) * 4;
       // element mask of this thread's 64 (query, key) pairs: built in a rolled loop so that the generic mask rule is
       // emitted once (boundary / flashmask blocks only); the hot loops below stay small enough for the instruction cache
       uint32_t mbits[2] = {0u, 0u};
       if (!full) {
-        if (mc.lts == nullptr) {  // seqlen tail / causal / window: the visible rows of a key column form an interval
+        if (mc.lts == nullptr || (kFM && !fm_partial)) {  // seqlen tail / causal / window: the visible rows of a key column form an interval
           int vlo, vhi;
           visible_rows(mc, col, vlo, vhi);
           mbits[0] = outside_bits(vlo, vhi, m0 + wg * 64);
@@ -560,7 +634,7 @@ bool out_ok(const fa_b200_tensor &t) {
   return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
 }
 
-template <int HD, bool kBf16> void launch_bwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM> void launch_bwd(const Params &p, cudaStream_t s) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
@@ -585,7 +659,8 @@ template <int HD, bool kBf16> void launch_bwd(const Params &p, cudaStream_t s) {
   }
   // 3. main kernel
   {
-    auto kern = bwd_kernel<HD, kBf16>;
+    if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
+    auto kern = bwd_kernel<HD, kBf16, kFM>;
     static bool attr_set = false;
     if (!attr_set) {
       FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
@@ -628,10 +703,13 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
 }
 
 void sm100_bwd(const Params &p, cudaStream_t s) {
+  const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
   if (p.d <= 64) {
-    if (p.is_bf16) launch_bwd<64, true>(p, s); else launch_bwd<64, false>(p, s);
+    if (p.is_bf16) { if (fm) launch_bwd<64, true, true>(p, s); else launch_bwd<64, true, false>(p, s); }
+    else { if (fm) launch_bwd<64, false, true>(p, s); else launch_bwd<64, false, false>(p, s); }
   } else {
-    if (p.is_bf16) launch_bwd<128, true>(p, s); else launch_bwd<128, false>(p, s);
+    if (p.is_bf16) { if (fm) launch_bwd<128, true, true>(p, s); else launch_bwd<128, true, false>(p, s); }
+    else { if (fm) launch_bwd<128, false, true>(p, s); else launch_bwd<128, false, false>(p, s); }
   }
 }
 

@@ -100,13 +100,95 @@ __device__ __forceinline__ void uniformize(TileInfo &ti) {
   for (int t = 0; t < 2; ++t) { ti.n_lo[t] = bcast0(ti.n_lo[t]); ti.n_hi[t] = bcast0(ti.n_hi[t]); }
 }
 
+// The ordered list of key blocks a work tile visits, as seen identically by every role (producer, MMA issuer, both
+// softmax warpgroups).  Without FlashMask it is the union range [lo, hi) of decode_tile.  With FlashMask (kFM) blocks
+// that the column-sparse mask covers completely for a Q tile are dropped for that tile, and blocks dropped for both Q
+// tiles are never loaded: the classification restates csrc/flashmask_v2/mainloop_fwd_sm90_tma_gmma_ws.hpp:835-853 on
+// the per-block min/max of the four vectors (flash_mask.hpp:162-245, computed by flashmask_scan_kernel with block 128).
+// The warp evaluates 32 blocks per step (one per lane) and ballots; all lanes hold the same state.
+struct Blk {
+  int j;
+  bool a[2];   // block takes part for Q tile t
+  bool pm[2];  // FlashMask may mask single elements of the block for Q tile t (needs the element rule)
+};
+template <bool kFM> struct BlockSeq {
+  int j, hi, nlo[2], nhi[2];
+  // FlashMask state
+  int base, r0[2], r1[2], lane;
+  uint32_t act[2], par[2];
+  const int32_t *mm;
+  int64_t plane;
+  bool has_lte, has_ute, has_uts;
+
+  __device__ __forceinline__ void init(const Params &p, const TileInfo &ti, int lane_) {
+    j = ti.lo; hi = ti.hi;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) { nlo[t] = ti.n_lo[t]; nhi[t] = ti.n_hi[t]; }
+    if constexpr (kFM) {
+      lane = lane_;
+      const int nbp = (ceil_div(p.seqlen_k, kBN) + 3) & ~3;
+      plane = (int64_t)p.b * p.h_mask * nbp;
+      mm = p.flashmask_maxmin + ((int64_t)ti.bi * p.h_mask + ti.hq / (p.h / p.h_mask)) * nbp;
+      has_lte = p.lt_end != nullptr; has_ute = p.ut_end != nullptr; has_uts = p.ut_start != nullptr;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) { r0[t] = ti.m0 + t * kBM; r1[t] = min(r0[t] + kBM, ti.sq); }
+      base = ti.lo - 32;
+      act[0] = act[1] = par[0] = par[1] = 0u;
+    }
+  }
+  __device__ __forceinline__ bool next(Blk &b) {
+    if constexpr (!kFM) {
+      if (j >= hi) return false;
+      b.j = j;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) { b.a[t] = j >= nlo[t] && j < nhi[t]; b.pm[t] = false; }
+      ++j;
+      return true;
+    } else {
+      while ((act[0] | act[1]) == 0u) {
+        base += 32;
+        if (base >= hi) return false;
+        const int jb = base + lane;
+        bool a_[2] = {false, false}, p_[2] = {false, false};
+        if (jb < hi) {
+          const int lts_max = mm[jb], lts_min = mm[plane + jb];
+          const int lte_max = has_lte ? mm[4 * plane + jb] : 0x7fffffff, lte_min = has_lte ? mm[5 * plane + jb] : 0x7fffffff;
+          const int ute_max = has_ute ? mm[2 * plane + jb] : 0, ute_min = has_ute ? mm[3 * plane + jb] : 0;
+          const int uts_max = has_uts ? mm[6 * plane + jb] : 0, uts_min = has_uts ? mm[7 * plane + jb] : 0;
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            const bool in = jb >= nlo[t] && jb < nhi[t];
+            const bool fully = (r0[t] >= lts_max && r1[t] <= lte_min) || (has_ute && r0[t] >= uts_max && r1[t] <= ute_min);
+            const bool clear = (r1[t] <= lts_min || r0[t] >= lte_max) && (!has_ute || r1[t] <= uts_min || r0[t] >= ute_max);
+            a_[t] = in && !fully;
+            p_[t] = a_[t] && !clear;
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          act[t] = __ballot_sync(0xffffffffu, a_[t]);
+          par[t] = __ballot_sync(0xffffffffu, p_[t]);
+        }
+      }
+      const int bit = __ffs(act[0] | act[1]) - 1;
+      b.j = base + bit;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        b.a[t] = (act[t] >> bit) & 1u; b.pm[t] = (par[t] >> bit) & 1u;
+        act[t] &= ~(1u << bit); par[t] &= ~(1u << bit);
+      }
+      return true;
+    }
+  }
+};
+
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 
-template <int HD, bool kBf16>
+template <int HD, bool kBf16, bool kFM>
 __global__ void __launch_bounds__(kThreads, 1)
 fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles) {
   using L = FwdSmem<HD>;
@@ -155,34 +237,44 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
    if (warp == 9) {
     // ======================= TMA producer =======================
-    if (lane == 0) {
+    // the whole warp walks the block sequence (FlashMask classification ballots); lane 0 waits and issues
+    {
       uint32_t kv_it = 0, qcnt[2] = {0, 0};
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         TileInfo ti;
         if (!decode_tile(p, tile, num_m, ti)) continue;
+        BlockSeq<kFM> seq;
+        seq.init(p, ti, lane);
+        bool q_loaded[2] = {false, false};
+        Blk blk;
+        while (seq.next(blk)) {
+          if (lane == 0) {
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (ti.n_hi[t] <= ti.n_lo[t]) continue;
-          mbar_wait(bar(B_QEMPTY + t), (qcnt[t] & 1) ^ 1);
-          mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
+            for (int t = 0; t < 2; ++t) {
+              if (!blk.a[t] || q_loaded[t]) continue;
+              mbar_wait(bar(B_QEMPTY + t), (qcnt[t] & 1) ^ 1);
+              mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
 #pragma unroll
-          for (int hf = 0; hf < kHalves; ++hf)
-            tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + hf * kHalfBytes, &tm.q, bar(B_QFULL + t), hf * 64, ti.hq,
-                        ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
-          ++qcnt[t];
-        }
-        for (int j = ti.lo; j < ti.hi; ++j) {
+              for (int hf = 0; hf < kHalves; ++hf)
+                tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + hf * kHalfBytes, &tm.q, bar(B_QFULL + t), hf * 64, ti.hq,
+                            ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
+              ++qcnt[t];
+            }
 #pragma unroll
-          for (int kv = 0; kv < 2; ++kv) {
-            const uint32_t st = kv_it % kStages, ph = (kv_it / kStages) & 1;
-            mbar_wait(bar(B_KVEMPTY + st), ph ^ 1);
-            mbar_expect_tx(bar(B_KVFULL + st), L::kTileBytes);
+            for (int kv = 0; kv < 2; ++kv) {
+              const uint32_t st = kv_it % kStages, ph = (kv_it / kStages) & 1;
+              mbar_wait(bar(B_KVEMPTY + st), ph ^ 1);
+              mbar_expect_tx(bar(B_KVFULL + st), L::kTileBytes);
 #pragma unroll
-            for (int hf = 0; hf < kHalves; ++hf)
-              tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + hf * kHalfBytes, kv == 0 ? &tm.k : &tm.v,
-                          bar(B_KVFULL + st), hf * 64, ti.hk, ti.k_row0 + j * kBN, ti.k_b);
-            ++kv_it;
+              for (int hf = 0; hf < kHalves; ++hf)
+                tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + hf * kHalfBytes, kv == 0 ? &tm.k : &tm.v,
+                            bar(B_KVFULL + st), hf * 64, ti.hk, ti.k_row0 + blk.j * kBN, ti.k_b);
+              ++kv_it;
+            }
           }
+#pragma unroll
+          for (int t = 0; t < 2; ++t) q_loaded[t] |= blk.a[t];
+          if constexpr (kFM) __syncwarp();
         }
       }
     }
@@ -228,53 +320,61 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         TileInfo ti;
         if (!bcast0(decode_tile(p, tile, num_m, ti) ? 1 : 0)) continue;
         uniformize(ti);
-        if (ti.hi <= ti.lo) continue;
-#pragma unroll
-        for (int t = 0; t < 2; ++t)
-          if (ti.n_hi[t] > ti.n_lo[t]) { mbar_wait(bar(B_QFULL + t), qcnt[t] & 1); ++qcnt[t]; }
+        BlockSeq<kFM> seq;
+        seq.init(p, ti, lane);
+        Blk cur, nxt;
+        if (!seq.next(cur)) continue;
+        bool q_ready[2] = {false, false}, first[2] = {true, true};
+        auto need_q = [&](int t) {
+          if (!q_ready[t]) { mbar_wait(bar(B_QFULL + t), qcnt[t] & 1); ++qcnt[t]; q_ready[t] = true; }
+        };
         // first K tile
         uint32_t kst = kv_it % kStages;
         mbar_wait(bar(B_KVFULL + kst), (kv_it / kStages) & 1);
         ++kv_it;
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+          if (cur.a[t]) need_q(t);
         tc_fence_after();
 #pragma unroll
         for (int t = 0; t < 2; ++t)
-          if (ti.lo >= ti.n_lo[t] && ti.lo < ti.n_hi[t]) issue_s(t, kst);
+          if (cur.a[t]) issue_s(t, kst);
         commit(bar(B_KVEMPTY + kst));
-        for (int j = ti.lo; j < ti.hi; ++j) {
+        bool have = true;
+        while (have) {
+          const bool has_next = seq.next(nxt);
           const uint32_t vst = kv_it % kStages;
           mbar_wait(bar(B_KVFULL + vst), (kv_it / kStages) & 1);
           ++kv_it;
-          const bool has_next = j + 1 < ti.hi;
           uint32_t nkst = 0;
           bool next_waited = false;
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
-            if (j >= ti.n_lo[t] && j < ti.n_hi[t]) {
+            if (cur.a[t]) {
               mbar_wait(bar(B_PFULL + t), pcnt[t] & 1);
               ++pcnt[t];
               tc_fence_after();
-              issue_pv(t, vst, j > ti.n_lo[t]);
+              issue_pv(t, vst, !first[t]);
+              first[t] = false;
             }
-            if (has_next && j + 1 >= ti.n_lo[t] && j + 1 < ti.n_hi[t]) {
+            if (has_next && nxt.a[t]) {
               if (!next_waited) {
                 nkst = kv_it % kStages;
                 mbar_wait(bar(B_KVFULL + nkst), (kv_it / kStages) & 1);
-                tc_fence_after();
                 next_waited = true;
               }
+              need_q(t);
+              tc_fence_after();
               issue_s(t, nkst);
             }
           }
           commit(bar(B_KVEMPTY + vst));
-          if (has_next) {
-            if (!next_waited) {  // no tile uses block j+1 (cannot happen for the union range, kept for safety)
-              nkst = kv_it % kStages;
-              mbar_wait(bar(B_KVFULL + nkst), (kv_it / kStages) & 1);
-            }
+          if (has_next) {   // a block of the sequence is active for at least one Q tile, so next_waited holds
             ++kv_it;
             commit(bar(B_KVEMPTY + nkst));
           }
+          cur = nxt;
+          have = has_next;
         }
       }
     }
@@ -295,24 +395,20 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       if (!decode_tile(p, tile, num_m, ti)) continue;
       if (!ti.active[t]) continue;
       const int row = ti.m0 + t * kBM + r_in_tile;
-      const int nlo = ti.n_lo[t], nhi = ti.n_hi[t];
       T *optr = (T *)p.o.ptr + (int64_t)ti.q_b * p.o.batch_stride + (int64_t)(ti.q_row0) * p.o.row_stride +
                 (int64_t)ti.hq * p.o.head_stride;
       float *lse_ptr = p.softmax_lse + ((int64_t)ti.bi * p.h + ti.hq) * p.seqlen_q;
-      if (nhi <= nlo) {
-        // no visible key block for this Q tile: out = 0, lse = +-inf
-        if (row < ti.sq) {
-          T *orow = optr + (int64_t)row * p.o.row_stride;
-          for (int e = 0; e < p.d; e += 8) *reinterpret_cast<uint4 *>(orow + e) = make_uint4(0, 0, 0, 0);
-          lse_ptr[row] = p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F;
-        }
-        continue;
-      }
       const MaskCtx mc = make_mask_ctx(p, ti.bi, ti.hq, ti.sq, ti.sk);
       const int shiftc = mc.bottom_right ? mc.shift : 0;
       const int r0 = ti.m0 + t * kBM;
       float m_ref = -CUDART_INF_F, l = 0.f;
-      for (int j = nlo; j < nhi; ++j) {
+      BlockSeq<kFM> seq;
+      seq.init(p, ti, lane);
+      Blk blk;
+      uint32_t nb = 0;   // blocks of this Q tile processed so far
+      while (seq.next(blk)) {
+        if (!blk.a[t]) continue;
+        const int j = blk.j;
         mbar_wait(bar(B_SFULL + t), scnt & 1);
         ++scnt;
         tc_fence_after();
@@ -323,12 +419,13 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         const int c0 = j * kBN;
         const bool full = (c0 + kBN <= ti.sk) && (!mc.causal || c0 + kBN - 1 <= r0 + shiftc) &&
                           (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
-                          (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) && (mc.lts == nullptr);
+                          (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) &&
+                          (kFM ? !blk.pm[t] : (mc.lts == nullptr));
         if (!full) {
           // boundary / flashmask blocks: the generic mask rule runs in a rolled loop (emitted once, keeps the hot loop
           // inside the instruction cache); the unrolled pass below only applies the resulting bit mask
           uint32_t mb[4];
-          if (mc.lts == nullptr) {  // seqlen tail / causal / window: the visible columns of a row form an interval
+          if (mc.lts == nullptr || (kFM && !blk.pm[t])) {  // seqlen tail / causal / window: the visible columns of a row form an interval
             int vlo, vhi;
             visible_cols(mc, row, vlo, vhi);
 #pragma unroll
@@ -355,13 +452,13 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
           mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
         }
         const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-        if (j == nlo) {
+        if (nb == 0) {
           m_ref = mx;
         } else {
           const bool need = (mx > m_ref) && ((mx - m_ref) * scale_log2 > kRescaleThreshold || m_ref == -CUDART_INF_F);
           if (__any_sync(0xffffffffu, need)) {
             // the previous PV of this tile must have landed in O before it is rescaled
-            mbar_wait(bar(B_OFULL + t), (ocnt + (uint32_t)(j - nlo - 1)) & 1);
+            mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
             tc_fence_after();
             const float m_new = fmaxf(m_ref, mx);
             const float corr = (m_new == -CUDART_INF_F) ? 1.f : ex2((m_ref - m_new) * scale_log2);
@@ -396,10 +493,20 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar(B_PFULL + t));
+        ++nb;
+      }
+      if (nb == 0) {
+        // no visible key block for this Q tile: out = 0, lse = +-inf (no barrier was touched)
+        if (row < ti.sq) {
+          T *orow = optr + (int64_t)row * p.o.row_stride;
+          for (int e = 0; e < p.d; e += 8) *reinterpret_cast<uint4 *>(orow + e) = make_uint4(0, 0, 0, 0);
+          lse_ptr[row] = p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F;
+        }
+        continue;
       }
       // ---------------- epilogue ----------------
-      mbar_wait(bar(B_OFULL + t), (ocnt + (uint32_t)(nhi - nlo - 1)) & 1);
-      ocnt += (uint32_t)(nhi - nlo);
+      mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
+      ocnt += nb;
       tc_fence_after();
       const float inv = (l > 0.f) ? 1.f / l : 0.f;
       uint8_t *stage = smem + L::kQOff + t * L::kTileBytes;  // Q_t is dead: all S MMAs of this tile have completed
@@ -475,7 +582,7 @@ bool tma_ok(const fa_b200_tensor &t, int heads, int batch) {
   return true;
 }
 
-template <int HD, bool kBf16> void launch_fwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM> void launch_fwd(const Params &p, cudaStream_t s) {
   using L = FwdSmem<HD>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
@@ -487,7 +594,8 @@ template <int HD, bool kBf16> void launch_fwd(const Params &p, cudaStream_t s) {
   tm.v = make_tma_4d(desc_for(p.v, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
-  auto kern = fwd_kernel<HD, kBf16>;
+  if (kFM) flashmask_prepare(p, kBN, s);   // per-128-key-block min/max of the mask vectors
+  auto kern = fwd_kernel<HD, kBf16, kFM>;
   static bool attr_set = false;
   if (!attr_set) {
     FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
@@ -520,10 +628,13 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
 }
 
 void sm100_fwd(const Params &p, cudaStream_t s) {
+  const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
   if (p.d <= 64) {
-    if (p.is_bf16) launch_fwd<64, true>(p, s); else launch_fwd<64, false>(p, s);
+    if (p.is_bf16) { if (fm) launch_fwd<64, true, true>(p, s); else launch_fwd<64, true, false>(p, s); }
+    else { if (fm) launch_fwd<64, false, true>(p, s); else launch_fwd<64, false, false>(p, s); }
   } else {
-    if (p.is_bf16) launch_fwd<128, true>(p, s); else launch_fwd<128, false>(p, s);
+    if (p.is_bf16) { if (fm) launch_fwd<128, true, true>(p, s); else launch_fwd<128, true, false>(p, s); }
+    else { if (fm) launch_fwd<128, false, true>(p, s); else launch_fwd<128, false, false>(p, s); }
   }
 }
 
