@@ -1,0 +1,8 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_features_gpu.py tests/test_flash_attn_gpu.py -m gpu -x -q > gpurun_out/pytest_feat.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_feat.log
+tail -5 gpurun_out/pytest_feat.log
+timeout 600 python tools/fm_probe.py c3 2>&1 | tee gpurun_out/fm_probe.log
+timeout 600 python tools/fm_probe.py long 2>&1 | tee -a gpurun_out/fm_probe.log
+timeout 600 python bench.py --workload c4 --steps 3 --warmup 2 > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err; tail -3 gpurun_out/bench_c4.err; python -c "
+import json; d=json.load(open('gpurun_out/bench_c4.json')); print('c4', d['encodings'])"

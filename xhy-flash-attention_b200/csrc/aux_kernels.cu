@@ -102,6 +102,36 @@ __global__ void __launch_bounds__(128) flashmask_scan_kernel(const Params p, int
   }
 }
 
+// Second level of the block scan: max-of-max / min-of-min over groups of 32 consecutive blocks, stored behind the eight
+// first-level planes (same order).  Lets the forward kernel discard 32 fully masked key blocks (4096 keys) per test
+// when a tile's causal range is long but the mask leaves only a narrow band (documents in a packed 256k-token row).
+__global__ void __launch_bounds__(128) flashmask_scan_l2_kernel(const Params p, int nblock_pad, int nsup) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int g = blockIdx.x * 4 + warp;
+  const int bh = blockIdx.y;
+  if (g >= nsup) return;
+  const int64_t plane = (int64_t)p.b * p.h_mask * nblock_pad;
+  const int64_t plane2 = (int64_t)p.b * p.h_mask * nsup;
+  int32_t *l2 = p.flashmask_maxmin + 8 * plane;
+  const bool present[4] = {p.lt_start != nullptr, p.ut_end != nullptr, p.lt_end != nullptr, p.ut_start != nullptr};
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    if (!present[v]) continue;
+    const int nb = g * 32 + lane;
+    int mx = 0, mn = INT_MAX;
+    if (nb < nblock_pad) {
+      mx = p.flashmask_maxmin[(2 * v) * plane + (int64_t)bh * nblock_pad + nb];
+      mn = p.flashmask_maxmin[(2 * v + 1) * plane + (int64_t)bh * nblock_pad + nb];
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    if (lane == 0) {
+      l2[(2 * v) * plane2 + (int64_t)bh * nsup + g] = mx;
+      l2[(2 * v + 1) * plane2 + (int64_t)bh * nsup + g] = mn;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // KV-cache append: cache[b, cache_seqlens[b] + i] = new[b, i]
 // (flash_attn_with_kvcache's k=/v=; csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1542 store_kv_new)
@@ -170,7 +200,7 @@ void combine_fwd(const Params &p, cudaStream_t s) {
   note_launch(1);
 }
 
-void flashmask_prepare(const Params &p, int block_n, cudaStream_t s) {
+void flashmask_prepare(const Params &p, int block_n, cudaStream_t s, bool with_l2) {
   FA_CHECK(block_n > 0, "flashmask_prepare: block_n must be positive");
   const int nblock = ceil_div(p.seqlen_k, block_n);
   const int nblock_pad = (nblock + 3) & ~3;
@@ -178,6 +208,13 @@ void flashmask_prepare(const Params &p, int block_n, cudaStream_t s) {
   flashmask_scan_kernel<<<grid, 128, 0, s>>>(p, block_n, nblock, nblock_pad);
   FA_CUDA(cudaGetLastError());
   note_launch(1);
+  if (with_l2 && flashmask_has_l2(p.seqlen_k, block_n)) {
+    const int nsup = ceil_div(nblock_pad, 32);
+    dim3 grid2(ceil_div(nsup, 4), p.b * p.h_mask);
+    flashmask_scan_l2_kernel<<<grid2, 128, 0, s>>>(p, nblock_pad, nsup);
+    FA_CUDA(cudaGetLastError());
+    note_launch(1);
+  }
 }
 
 void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,

@@ -59,7 +59,7 @@ void sm100_bwd(const Params &p, cudaStream_t s);
 // bandwidth kernels
 void splitkv_fwd(const Params &p, cudaStream_t s);
 void combine_fwd(const Params &p, cudaStream_t s);
-void flashmask_prepare(const Params &p, int block_n, cudaStream_t s);
+void flashmask_prepare(const Params &p, int block_n, cudaStream_t s, bool with_l2 = false);
 void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,
                int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16,
                int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s);
@@ -76,6 +76,14 @@ struct SeqInfo {
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+// The flashmask_maxmin workspace is sized by the caller for 64-key blocks (8 * b * h_mask * round_up(ceil(sk/64), 4)
+// int32, the reference's contract).  The tcgen05 kernels scan with 128-key blocks, which leaves room behind the eight
+// first-level planes for a second level over groups of 32 blocks whenever this holds.
+__host__ __device__ inline bool flashmask_has_l2(int seqlen_k, int block_n) {
+  const int nbp = (ceil_div(seqlen_k, block_n) + 3) & ~3;
+  const int nbp64 = (ceil_div(seqlen_k, 64) + 3) & ~3;
+  return block_n >= 128 && nbp + ceil_div(nbp, 32) <= nbp64;
+}
 
 #ifdef __CUDACC__
 // Restates csrc/flash_attn/src/block_info.h:12-37 (sum_s = cu_seqlens[b], actual = cu[b+1]-cu[b];

@@ -419,11 +419,23 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
       // emitted once (boundary / flashmask blocks only); the hot loops below stay small enough for the instruction cache
       uint32_t mbits[2] = {0u, 0u};
       if (!full) {
-        if (mc.lts == nullptr || (kFM && !fm_partial)) {  // seqlen tail / causal / window: the visible rows of a key column form an interval
+        if (mc.lts == nullptr || kFM) {  // seqlen tail / causal / window: the visible rows of a key column form an interval
           int vlo, vhi;
           visible_rows(mc, col, vlo, vhi);
           mbits[0] = outside_bits(vlo, vhi, m0 + wg * 64);
           mbits[1] = outside_bits(vlo, vhi, m0 + wg * 64 + 32);
+          if (kFM && fm_partial && col < t.sk) {
+            // FlashMask element rule for this thread's key column: the masked rows are the two intervals
+            // [lts, lte) and [uts, ute), so the bit masks follow arithmetically
+            const int lts_ = mc.lts[col], lte_ = mc.lte ? mc.lte[col] : 0x7fffffff;
+            mbits[0] |= ~outside_bits(lts_, lte_, m0 + wg * 64);
+            mbits[1] |= ~outside_bits(lts_, lte_, m0 + wg * 64 + 32);
+            if (mc.ute) {
+              const int uts_ = mc.uts ? mc.uts[col] : 0, ute_ = mc.ute[col];
+              mbits[0] |= ~outside_bits(uts_, ute_, m0 + wg * 64);
+              mbits[1] |= ~outside_bits(uts_, ute_, m0 + wg * 64 + 32);
+            }
+          }
         } else {
 #pragma unroll 1
           for (int i = 0; i < 64; ++i)

@@ -43,7 +43,11 @@ template <int HD> struct FwdSmem {
   static constexpr int kBarOff = kKVOff + kStages * kTileBytes;
   static constexpr int kNumBars = 2 + 2 + kStages * 2 + 2 + 2 + 2;
   static constexpr int kTmemSlotOff = kBarOff + kNumBars * 8;
-  static constexpr int kTotal = kTmemSlotOff + 16;
+  // FlashMask: record ring + its barriers, and per softmax warpgroup the staged mask vectors of one key block
+  static constexpr int kFmRecOff = (kTmemSlotOff + 16 + 31) / 32 * 32;
+  static constexpr int kFmBarOff = kFmRecOff + 16 * 32;
+  static constexpr int kFmVecOff = kFmBarOff + 2 * 16 * 8;
+  static constexpr int kTotal = kFmVecOff + 2 * 4 * kBN * 4;
   static constexpr int kDynBytes = kTotal + 1024;               // slack for manual 1024-byte alignment
 };
 
@@ -105,36 +109,36 @@ __device__ __forceinline__ void uniformize(TileInfo &ti) {
 // that the column-sparse mask covers completely for a Q tile are dropped for that tile, and blocks dropped for both Q
 // tiles are never loaded: the classification restates csrc/flashmask_v2/mainloop_fwd_sm90_tma_gmma_ws.hpp:835-853 on
 // the per-block min/max of the four vectors (flash_mask.hpp:162-245, computed by flashmask_scan_kernel with block 128).
-// The warp evaluates 32 blocks per step (one per lane) and ballots; all lanes hold the same state.
+//
+// The classification reads global memory, so it is done AHEAD of the consumers by a dedicated scanner warp (warp 10),
+// 32 blocks per step (one per lane, results balloted), and published as records in a shared-memory ring guarded by
+// full/empty mbarriers -- the reference uses generator warps the same way (flash_fwd_kernel_sm90.h:435).  A record is
+// {first block of the 32-group, active bits for Q tile 0 / 1, partial bits for Q tile 0 / 1}; base < 0 ends a tile.
+// Every consumer warp (producer, issuer, 8 softmax warps) reads every record.
+constexpr int kFmRing = 16;        // records in flight
+constexpr int kFmConsumers = 10;   // warps that read each record
 struct Blk {
   int j;
   bool a[2];   // block takes part for Q tile t
   bool pm[2];  // FlashMask may mask single elements of the block for Q tile t (needs the element rule)
 };
+struct FmRing {
+  uint32_t rec, full, empty;   // shared-memory addresses: records (8 x u32 each), full barriers, empty barriers
+};
 template <bool kFM> struct BlockSeq {
   int j, hi, nlo[2], nhi[2];
-  // FlashMask state
-  int base, r0[2], r1[2], lane;
-  uint32_t act[2], par[2];
-  const int32_t *mm;
-  int64_t plane;
-  bool has_lte, has_ute, has_uts;
+  // FlashMask consumer state
+  FmRing ring;
+  uint32_t rec_it, act[2], par[2];
+  int base, lane;
+  bool done;
 
-  __device__ __forceinline__ void init(const Params &p, const TileInfo &ti, int lane_) {
+  __device__ __forceinline__ void setup(const FmRing &r, int lane_) { ring = r; rec_it = 0; lane = lane_; }
+  __device__ __forceinline__ void init(const Params &p, const TileInfo &ti) {
     j = ti.lo; hi = ti.hi;
 #pragma unroll
     for (int t = 0; t < 2; ++t) { nlo[t] = ti.n_lo[t]; nhi[t] = ti.n_hi[t]; }
-    if constexpr (kFM) {
-      lane = lane_;
-      const int nbp = (ceil_div(p.seqlen_k, kBN) + 3) & ~3;
-      plane = (int64_t)p.b * p.h_mask * nbp;
-      mm = p.flashmask_maxmin + ((int64_t)ti.bi * p.h_mask + ti.hq / (p.h / p.h_mask)) * nbp;
-      has_lte = p.lt_end != nullptr; has_ute = p.ut_end != nullptr; has_uts = p.ut_start != nullptr;
-#pragma unroll
-      for (int t = 0; t < 2; ++t) { r0[t] = ti.m0 + t * kBM; r1[t] = min(r0[t] + kBM, ti.sq); }
-      base = ti.lo - 32;
-      act[0] = act[1] = par[0] = par[1] = 0u;
-    }
+    if constexpr (kFM) { act[0] = act[1] = par[0] = par[1] = 0u; done = false; base = 0; }
   }
   __device__ __forceinline__ bool next(Blk &b) {
     if constexpr (!kFM) {
@@ -146,29 +150,18 @@ template <bool kFM> struct BlockSeq {
       return true;
     } else {
       while ((act[0] | act[1]) == 0u) {
-        base += 32;
-        if (base >= hi) return false;
-        const int jb = base + lane;
-        bool a_[2] = {false, false}, p_[2] = {false, false};
-        if (jb < hi) {
-          const int lts_max = mm[jb], lts_min = mm[plane + jb];
-          const int lte_max = has_lte ? mm[4 * plane + jb] : 0x7fffffff, lte_min = has_lte ? mm[5 * plane + jb] : 0x7fffffff;
-          const int ute_max = has_ute ? mm[2 * plane + jb] : 0, ute_min = has_ute ? mm[3 * plane + jb] : 0;
-          const int uts_max = has_uts ? mm[6 * plane + jb] : 0, uts_min = has_uts ? mm[7 * plane + jb] : 0;
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const bool in = jb >= nlo[t] && jb < nhi[t];
-            const bool fully = (r0[t] >= lts_max && r1[t] <= lte_min) || (has_ute && r0[t] >= uts_max && r1[t] <= ute_min);
-            const bool clear = (r1[t] <= lts_min || r0[t] >= lte_max) && (!has_ute || r1[t] <= uts_min || r0[t] >= ute_max);
-            a_[t] = in && !fully;
-            p_[t] = a_[t] && !clear;
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          act[t] = __ballot_sync(0xffffffffu, a_[t]);
-          par[t] = __ballot_sync(0xffffffffu, p_[t]);
-        }
+        if (done) return false;
+        const uint32_t slot = rec_it % kFmRing;
+        mbar_wait(ring.full + slot * 8, (rec_it / kFmRing) & 1);
+        uint32_t r0, r1, r2, r3, r4;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(ring.rec + slot * 32));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r4) : "r"(ring.rec + slot * 32 + 16));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(ring.empty + slot * 8);
+        ++rec_it;
+        base = (int)r0;
+        if (base < 0) { done = true; return false; }
+        act[0] = r1; act[1] = r2; par[0] = r3; par[1] = r4;
       }
       const int bit = __ffs(act[0] | act[1]) - 1;
       b.j = base + bit;
@@ -180,7 +173,81 @@ template <bool kFM> struct BlockSeq {
       return true;
     }
   }
+  // a consumer that leaves a tile early must still drain its records (not used today: every role walks to the end)
 };
+
+// Scanner (one warp): classifies the key blocks of every work tile of this CTA and publishes the records.
+// Two levels: groups of 32 blocks are first tested against the group-wide min/max (flashmask_scan_l2_kernel) so that a
+// long causal range with a narrow visible band (documents in a 256k-token row) costs one test per 4096 keys.
+__device__ __forceinline__ void fm_scan_tile(const Params &p, const TileInfo &ti, const FmRing &ring, uint32_t &rec_it, int lane) {
+  const int nbp = (ceil_div(p.seqlen_k, kBN) + 3) & ~3;
+  const int64_t plane = (int64_t)p.b * p.h_mask * nbp;
+  const int64_t row = (int64_t)ti.bi * p.h_mask + ti.hq / (p.h / p.h_mask);
+  const int32_t *mm = p.flashmask_maxmin + row * nbp;
+  const bool has_lte = p.lt_end != nullptr, has_ute = p.ut_end != nullptr, has_uts = p.ut_start != nullptr;
+  const bool has_l2 = flashmask_has_l2(p.seqlen_k, kBN);
+  const int nsup = ceil_div(nbp, 32);
+  const int64_t plane2 = (int64_t)p.b * p.h_mask * nsup;
+  const int32_t *mm2 = p.flashmask_maxmin + 8 * plane + row * nsup;
+  int r0[2], r1[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) { r0[t] = ti.m0 + t * kBM; r1[t] = min(r0[t] + kBM, ti.sq); }
+  auto publish = [&](int base, uint32_t a0, uint32_t a1, uint32_t p0, uint32_t p1) {
+    const uint32_t slot = rec_it % kFmRing;
+    mbar_wait(ring.empty + slot * 8, ((rec_it / kFmRing) & 1) ^ 1);
+    if (lane == 0) {
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(ring.rec + slot * 32), "r"((uint32_t)base), "r"(a0), "r"(a1), "r"(p0) : "memory");
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(ring.rec + slot * 32 + 16), "r"(p1) : "memory");
+      mbar_arrive(ring.full + slot * 8);
+    }
+    __syncwarp();
+    ++rec_it;
+  };
+  for (int wbase = ti.lo / 32; wbase * 32 < ti.hi; wbase += 32) {   // window of 32 groups
+    const int g = wbase + lane;
+    bool cand = g * 32 < ti.hi;
+    if (cand && has_l2) {
+      const int lts_max = mm2[g];
+      const int lte_min = has_lte ? mm2[5 * plane2 + g] : 0x7fffffff;
+      const int ute_min = has_ute ? mm2[3 * plane2 + g] : 0;
+      const int uts_max = has_uts ? mm2[6 * plane2 + g] : 0;
+      bool all_full = true;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        const bool in = ti.n_hi[t] > ti.n_lo[t];
+        const bool fully = (r0[t] >= lts_max && r1[t] <= lte_min) || (has_ute && r0[t] >= uts_max && r1[t] <= ute_min);
+        all_full = all_full && (!in || fully);
+      }
+      cand = !all_full;
+    }
+    uint32_t sup = __ballot_sync(0xffffffffu, cand);
+    while (sup) {
+      const int gbit = __ffs(sup) - 1;
+      sup &= sup - 1;
+      const int base = (wbase + gbit) * 32;
+      const int jb = base + lane;
+      bool a_[2] = {false, false}, p_[2] = {false, false};
+      if (jb >= ti.lo && jb < ti.hi) {
+        const int lts_max = mm[jb], lts_min = mm[plane + jb];
+        const int lte_max = has_lte ? mm[4 * plane + jb] : 0x7fffffff, lte_min = has_lte ? mm[5 * plane + jb] : 0x7fffffff;
+        const int ute_max = has_ute ? mm[2 * plane + jb] : 0, ute_min = has_ute ? mm[3 * plane + jb] : 0;
+        const int uts_max = has_uts ? mm[6 * plane + jb] : 0, uts_min = has_uts ? mm[7 * plane + jb] : 0;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          const bool in = jb >= ti.n_lo[t] && jb < ti.n_hi[t];
+          const bool fully = (r0[t] >= lts_max && r1[t] <= lte_min) || (has_ute && r0[t] >= uts_max && r1[t] <= ute_min);
+          const bool clear = (r1[t] <= lts_min || r0[t] >= lte_max) && (!has_ute || r1[t] <= uts_min || r0[t] >= ute_max);
+          a_[t] = in && !fully;
+          p_[t] = a_[t] && !clear;
+        }
+      }
+      const uint32_t a0 = __ballot_sync(0xffffffffu, a_[0]), a1 = __ballot_sync(0xffffffffu, a_[1]);
+      const uint32_t p0 = __ballot_sync(0xffffffffu, p_[0]), p1 = __ballot_sync(0xffffffffu, p_[1]);
+      if ((a0 | a1) != 0u) publish(base, a0, a1, p0, p1);
+    }
+  }
+  publish(-1, 0u, 0u, 0u, 0u);   // end of tile
+}
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -202,6 +269,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
   const int B_QFULL = 0, B_QEMPTY = 2, B_KVFULL = 4, B_KVEMPTY = 4 + kStages, B_SFULL = 4 + 2 * kStages,
             B_PFULL = B_SFULL + 2, B_OFULL = B_PFULL + 2;
   uint32_t *tmem_slot = (uint32_t *)(smem + L::kTmemSlotOff);
+  const FmRing fm_ring = {sbase + L::kFmRecOff, sbase + L::kFmBarOff, sbase + L::kFmBarOff + kFmRing * 8};
 
   if (threadIdx.x == 0) {
     for (int t = 0; t < 2; ++t) {
@@ -214,6 +282,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bar(B_KVFULL + s), 1);
       mbar_init(bar(B_KVEMPTY + s), 1);
+    }
+    if constexpr (kFM) {
+      for (int r = 0; r < kFmRing; ++r) {
+        mbar_init(sbase + L::kFmBarOff + r * 8, 1);
+        mbar_init(sbase + L::kFmBarOff + (kFmRing + r) * 8, kFmConsumers);
+      }
     }
     fence_mbar_init();
   }
@@ -240,11 +314,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     // the whole warp walks the block sequence (FlashMask classification ballots); lane 0 waits and issues
     {
       uint32_t kv_it = 0, qcnt[2] = {0, 0};
+      BlockSeq<kFM> seq;
+      seq.setup(fm_ring, lane);
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         TileInfo ti;
         if (!decode_tile(p, tile, num_m, ti)) continue;
-        BlockSeq<kFM> seq;
-        seq.init(p, ti, lane);
+        seq.init(p, ti);
         bool q_loaded[2] = {false, false};
         Blk blk;
         while (seq.next(blk)) {
@@ -316,12 +391,13 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         }
         __syncwarp();
       };
+      BlockSeq<kFM> seq;
+      seq.setup(fm_ring, lane);
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         TileInfo ti;
         if (!bcast0(decode_tile(p, tile, num_m, ti) ? 1 : 0)) continue;
         uniformize(ti);
-        BlockSeq<kFM> seq;
-        seq.init(p, ti, lane);
+        seq.init(p, ti);
         Blk cur, nxt;
         if (!seq.next(cur)) continue;
         bool q_ready[2] = {false, false}, first[2] = {true, true};
@@ -378,6 +454,16 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         }
       }
     }
+   } else if (warp == 10) {
+    // ======================= FlashMask scanner =======================
+    if constexpr (kFM) {
+      uint32_t rec_it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        TileInfo ti;
+        if (!decode_tile(p, tile, num_m, ti)) continue;
+        fm_scan_tile(p, ti, fm_ring, rec_it, lane);
+      }
+    }
    }
   } else {
     // ======================= softmax warpgroups =======================
@@ -390,10 +476,19 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     const float scale_log2 = p.softmax_scale * kLog2e;
     uint32_t scnt = 0, ocnt = 0;
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    BlockSeq<kFM> seq;
+    seq.setup(fm_ring, lane);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       TileInfo ti;
       if (!decode_tile(p, tile, num_m, ti)) continue;
-      if (!ti.active[t]) continue;
+      if (!ti.active[t]) {
+        if constexpr (kFM) {   // the records of this tile must still be consumed
+          seq.init(p, ti);
+          Blk skip;
+          while (seq.next(skip)) {}
+        }
+        continue;
+      }
       const int row = ti.m0 + t * kBM + r_in_tile;
       T *optr = (T *)p.o.ptr + (int64_t)ti.q_b * p.o.batch_stride + (int64_t)(ti.q_row0) * p.o.row_stride +
                 (int64_t)ti.hq * p.o.head_stride;
@@ -402,8 +497,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       const int shiftc = mc.bottom_right ? mc.shift : 0;
       const int r0 = ti.m0 + t * kBM;
       float m_ref = -CUDART_INF_F, l = 0.f;
-      BlockSeq<kFM> seq;
-      seq.init(p, ti, lane);
+      seq.init(p, ti);
       Blk blk;
       uint32_t nb = 0;   // blocks of this Q tile processed so far
       while (seq.next(blk)) {
@@ -425,11 +519,56 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
           // boundary / flashmask blocks: the generic mask rule runs in a rolled loop (emitted once, keeps the hot loop
           // inside the instruction cache); the unrolled pass below only applies the resulting bit mask
           uint32_t mb[4];
-          if (mc.lts == nullptr || (kFM && !blk.pm[t])) {  // seqlen tail / causal / window: the visible columns of a row form an interval
+          if (mc.lts == nullptr || kFM) {  // seqlen tail / causal / window: the visible columns of a row form an interval
             int vlo, vhi;
             visible_cols(mc, row, vlo, vhi);
 #pragma unroll
             for (int c = 0; c < 4; ++c) mb[c] = outside_bits(vlo, vhi, c0 + c * 32);
+            if (kFM && blk.pm[t]) {
+              // FlashMask element rule for a partially masked block: the warpgroup stages the block's 128 entries of
+              // each vector in shared memory (one per thread), then every thread tests its row against all columns
+              const uint32_t vec = sbase + L::kFmVecOff + t * (4 * kBN * 4);
+              named_bar_sync(3 + t, kBM);   // the previous partial block has been read out
+              {
+                const int col = c0 + r_in_tile;
+                const bool ok = col < ti.sk;
+                const int lts_ = ok ? mc.lts[col] : 0x7fffffff;
+                const int lte_ = ok ? (mc.lte ? mc.lte[col] : 0x7fffffff) : 0x7fffffff;
+                const int ute_ = ok && mc.ute ? mc.ute[col] : 0;
+                const int uts_ = ok && mc.ute && mc.uts ? mc.uts[col] : 0;
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(vec + (0 * kBN + r_in_tile) * 4), "r"(lts_) : "memory");
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(vec + (1 * kBN + r_in_tile) * 4), "r"(lte_) : "memory");
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(vec + (2 * kBN + r_in_tile) * 4), "r"(uts_) : "memory");
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(vec + (3 * kBN + r_in_tile) * 4), "r"(ute_) : "memory");
+              }
+              named_bar_sync(3 + t, kBM);
+              const bool two_bands = mc.ute != nullptr;
+              uint32_t w0 = 0u, w1 = 0u, w2 = 0u, w3 = 0u;
+#pragma unroll 1
+              for (int c = 0; c < 4; ++c) {
+                uint32_t word = 0u;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                  const float4 a = lds128(vec + (0 * kBN + c * 32 + i) * 4), b4 = lds128(vec + (1 * kBN + c * 32 + i) * 4);
+                  const int as[4] = {__float_as_int(a.x), __float_as_int(a.y), __float_as_int(a.z), __float_as_int(a.w)};
+                  const int bs[4] = {__float_as_int(b4.x), __float_as_int(b4.y), __float_as_int(b4.z), __float_as_int(b4.w)};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) word |= (row >= as[e] && row < bs[e]) ? (1u << (i + e)) : 0u;
+                }
+                if (two_bands) {
+#pragma unroll
+                  for (int i = 0; i < 32; i += 4) {
+                    const float4 a = lds128(vec + (2 * kBN + c * 32 + i) * 4), b4 = lds128(vec + (3 * kBN + c * 32 + i) * 4);
+                    const int as[4] = {__float_as_int(a.x), __float_as_int(a.y), __float_as_int(a.z), __float_as_int(a.w)};
+                    const int bs[4] = {__float_as_int(b4.x), __float_as_int(b4.y), __float_as_int(b4.z), __float_as_int(b4.w)};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) word |= (row >= as[e] && row < bs[e]) ? (1u << (i + e)) : 0u;
+                  }
+                }
+                w0 = c == 0 ? word : w0; w1 = c == 1 ? word : w1; w2 = c == 2 ? word : w2; w3 = c == 3 ? word : w3;
+              }
+              mb[0] |= w0; mb[1] |= w1; mb[2] |= w2; mb[3] |= w3;
+            }
           } else {
 #pragma unroll
             for (int c = 0; c < 4; ++c) mb[c] = 0u;
@@ -594,7 +733,7 @@ template <int HD, bool kBf16, bool kFM> void launch_fwd(const Params &p, cudaStr
   tm.v = make_tma_4d(desc_for(p.v, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
-  if (kFM) flashmask_prepare(p, kBN, s);   // per-128-key-block min/max of the mask vectors
+  if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
   auto kern = fwd_kernel<HD, kBf16, kFM>;
   static bool attr_set = false;
   if (!attr_set) {
