@@ -14,7 +14,8 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libflashattn_b200.so")
+# FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
+LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
 FA_B200_ABI_VERSION = 1
 

@@ -172,6 +172,16 @@ template <bool kFM> struct MCursor {
       }
     }
   }
+  // Position of iteration `it` (called with it = 0, 1, 2, ... in order).  Without FlashMask this is the closed form the
+  // counted loops always used (keeps their code generation); with FlashMask the cursor walks the surviving ranges.
+  __device__ __forceinline__ void step(const Params &p, const BwdTile &t, int it) {
+    if constexpr (!kFM) {
+      const int nm = t.m_hi - t.m_lo;
+      hq = t.hq0 + it / nm; m = t.m_lo + it % nm;
+    } else {
+      next(p, t);
+    }
+  }
   // may FlashMask mask single elements of query block m (for this key block)?
   __device__ __forceinline__ bool partial(const BwdTile &t) const {
     if constexpr (!kFM) return false;
@@ -198,9 +208,10 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
   BwdTile t;
   const bool live = bwd_decode(p, t);
   if (!live) return;  // uniform for the whole CTA
-  int n_it = 0;
-  {
+  int n_it = (t.hq1 - t.hq0) * (t.m_hi - t.m_lo);
+  if constexpr (kFM) {
     MCursor<kFM> c;
+    n_it = 0;
     for (int h = t.hq0; h < t.hq1; ++h) { c.load_head(p, t, h); n_it += c.count(); }
   }
   const int n_it_u = __shfl_sync(0xffffffffu, n_it, 0);  // same value, provably warp-uniform for the issuer warp
@@ -243,7 +254,8 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
       }
       MCursor<kFM> cur;
       cur.init(t);
-      for (int it = 0; cur.next(p, t); ++it) {
+      for (int it = 0; it < n_it; ++it) {
+        cur.step(p, t, it);
         const int st = it & 1;
         const int hq = cur.hq, m = cur.m;
         mbar_wait(bar(BB_Q_EMPTY + st), ((it >> 1) & 1) ^ 1);
@@ -356,7 +368,8 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     uint32_t g = 0;  // bulk groups committed so far; group g uses staging buffer g & 1, last used by group g - 2
     MCursor<kFM> cur;
     cur.init(t);
-    for (int it = 0; cur.next(p, t); ++it) {
+    for (int it = 0; it < n_it; ++it) {
+      cur.step(p, t, it);
       const int hq = cur.hq, m = cur.m;
       float *gtile = p.dq_accum + acc_tile_index(p, t, hq, m) * (int64_t)(p.d_rounded / 32) * (kB * 32);
       mbar_wait(bar(BB_DQ_FULL), it & 1);
@@ -403,7 +416,8 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     const int shiftc = p.causal_bottom_right ? shift : 0;
     MCursor<kFM> cur;
     cur.init(t);
-    for (int it = 0; cur.next(p, t); ++it) {
+    for (int it = 0; it < n_it; ++it) {
+      cur.step(p, t, it);
       const int st = it & 1;
       const int hq = cur.hq, m = cur.m;
       const int m0 = m * kB;
@@ -556,11 +570,22 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
 // (csrc/flash_attn/src/flash_bwd_kernel.h:112-188)
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) bwd_dpsum_kernel(const Params p) {
+__global__ void __launch_bounds__(256) bwd_dpsum_kernel(const Params p, int64_t acc_vec4) {
+  // (a) zero the fp32 dQ accumulator (grid-stride, 16-byte stores): fused here so that the write stream overlaps the
+  //     O / dO read stream of (b) instead of costing a separate memset pass
+  {
+    const int64_t nthreads = (int64_t)gridDim.x * gridDim.y * gridDim.z * 256;
+    const int64_t tid = (((int64_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 256 + threadIdx.x;
+    float4 *acc = reinterpret_cast<float4 *>(p.dq_accum);
+#ifndef FA_AB_MEMSET
+    for (int64_t i = tid; i < acc_vec4; i += nthreads) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#endif
+  }
+  // (b) dPsum: 16 lanes per row (8 elements each cover d <= 128), two rows per warp, 16 rows per block
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int sub = lane / 16, l16 = lane % 16;
   const int hq = blockIdx.y, bi = blockIdx.z;
-  const int row = blockIdx.x * 8 + warp;
-  if (row >= p.seqlen_q_rounded) return;
+  const int row = blockIdx.x * 16 + warp * 2 + sub;
   int q_row0, sq, k_row0, sk;
   bool qb, kb;
   seq_bounds(p, bi, q_row0, sq, k_row0, sk, qb, kb);
@@ -570,7 +595,7 @@ __global__ void __launch_bounds__(256) bwd_dpsum_kernel(const Params p) {
                  (int64_t)hq * p.o.head_stride;
     const T *g = (const T *)p.dout.ptr + (qb ? bi : 0) * p.dout.batch_stride +
                  (int64_t)(q_row0 + row) * p.dout.row_stride + (int64_t)hq * p.dout.head_stride;
-    for (int e = lane * 8; e < p.d; e += 256) {
+    for (int e = l16 * 8; e < p.d; e += 128) {
       const uint4 a = *reinterpret_cast<const uint4 *>(o + e);
       const uint4 b = *reinterpret_cast<const uint4 *>(g + e);
       const T *ae = reinterpret_cast<const T *>(&a);
@@ -578,10 +603,10 @@ __global__ void __launch_bounds__(256) bwd_dpsum_kernel(const Params p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc = fmaf((float)ae[i], (float)be[i], acc);
     }
-#pragma unroll
-    for (int o2 = 16; o2 > 0; o2 >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o2);
   }
-  if (lane == 0) p.softmax_d[((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row] = acc;
+#pragma unroll
+  for (int o2 = 8; o2 > 0; o2 >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o2);
+  if (l16 == 0 && row < p.seqlen_q_rounded) p.softmax_d[((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row] = acc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -655,19 +680,19 @@ template <int HD, bool kBf16, bool kFM> void launch_bwd(const Params &p, cudaStr
   tm.dout = make_tma_4d(bdesc(p.dout, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b));
   tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
   tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
-  // 1. dPsum
-  {
-    dim3 grid(ceil_div(p.seqlen_q_rounded, 8), p.h, p.b);
-    bwd_dpsum_kernel<T><<<grid, 256, 0, s>>>(p);
-    FA_CUDA(cudaGetLastError());
-    note_launch(2);
-  }
-  // 2. zero the fp32 dQ accumulator
+  // 1. dPsum + zeroing of the fp32 dQ accumulator (one kernel)
   {
     int64_t tiles;
     if (packed) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
     else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
-    FA_CUDA(cudaMemsetAsync(p.dq_accum, 0, (size_t)tiles * (p.d_rounded / 32) * (kB * 32) * sizeof(float), s));
+    const int64_t acc_vec4 = tiles * (p.d_rounded / 32) * (kB * 32) / 4;
+    dim3 grid(ceil_div(p.seqlen_q_rounded, 16), p.h, p.b);
+#ifdef FA_AB_MEMSET
+    FA_CUDA(cudaMemsetAsync(p.dq_accum, 0, (size_t)acc_vec4 * 16, s));
+#endif
+    bwd_dpsum_kernel<T><<<grid, 256, 0, s>>>(p, acc_vec4);
+    FA_CUDA(cudaGetLastError());
+    note_launch(2);
   }
   // 3. main kernel
   {

@@ -255,6 +255,48 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// ---- packed fp32x2 arithmetic (FFMA2 / FADD2: two elements per issue slot) ----
+__device__ __forceinline__ uint64_t pk2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(uint64_t v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// 2^x for a pair, on the FMA pipe instead of the MUFU: x = j + f with j = round(x), f in [-0.5, 0.5];
+// 2^f by a degree-3 polynomial (max relative error 7.7e-5, well below the 16-bit rounding of P), 2^j by adding j to the
+// exponent field.  The forward softmax is MUFU-bound on B200 (16 ex2/clk/SM against 8192 tensor flop/clk/SM at d128:
+// the exponentials take as long as the MMAs), so a quarter of the exponentials are moved here.
+__device__ __forceinline__ void exp2_poly2(uint64_t x2, float &p0, float &p1) {
+  float x0, x1;
+  unpk2(x2, x0, x1);
+  x0 = fmaxf(x0, -125.f); x1 = fmaxf(x1, -125.f);   // keeps the result a normal number (and maps -inf to ~0)
+  const uint64_t xc = pk2(x0, x1);
+  const uint64_t magic = pk2(12582912.f, 12582912.f);           // 1.5 * 2^23: low mantissa bits = round(x)
+  const uint64_t jm = fadd2(xc, magic);
+  const uint64_t jf = fadd2(jm, pk2(-12582912.f, -12582912.f)); // float(j)
+  const uint64_t f = ffma2(jf, pk2(-1.f, -1.f), xc);            // x - j
+  uint64_t q = ffma2(pk2(0.05508868396282196f, 0.05508868396282196f), f, pk2(0.24260404706001282f, 0.24260404706001282f));
+  q = ffma2(q, f, pk2(0.6932762265205383f, 0.6932762265205383f));
+  q = ffma2(q, f, pk2(0.9999289512634277f, 0.9999289512634277f));
+  float q0, q1, j0, j1;
+  unpk2(q, q0, q1);
+  unpk2(jm, j0, j1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(j0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(j1) << 23));
+}
+
 template <int HD, bool kBf16, bool kFM>
 __global__ void __launch_bounds__(kThreads, 1)
 fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles) {
@@ -615,20 +657,32 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
           }
         }
         const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
-        float sum0 = 0.f, sum1 = 0.f;
+        const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
+        uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const float p0 = ex2(fmaf(__uint_as_float(s[c][2 * i]), scale_log2, -msc));
-            const float p1 = ex2(fmaf(__uint_as_float(s[c][2 * i + 1]), scale_log2, -msc));
-            sum0 += p0; sum1 += p1;
+            const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
+            float p0, p1;
+            if (i % 4 == 3) {          // every fourth pair: polynomial on the FMA pipe
+              exp2_poly2(x2, p0, p1);
+            } else {
+              float x0, x1;
+              unpk2(x2, x0, x1);
+              p0 = ex2(x0); p1 = ex2(x1);
+            }
+            if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
             pk[i] = pack2<kBf16>(p0, p1);
           }
           tmem_st16(tS + c * 16, pk);
         }
-        l += sum0 + sum1;
+        {
+          float a0, a1;
+          unpk2(fadd2(suma, sumb), a0, a1);
+          l += a0 + a1;
+        }
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar(B_PFULL + t));
@@ -647,7 +701,10 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
       ocnt += nb;
       tc_fence_after();
-      const float inv = (l > 0.f) ? 1.f / l : 0.f;
+      // A row with at least one visible key has l >= ~1 (its maximum contributes 2^0).  Masked elements that went
+      // through the polynomial exp2 contribute 2^-125 each instead of 0, so "no visible key" is l below a tiny bound.
+      const bool nonempty = l > 1e-30f;
+      const float inv = nonempty ? 1.f / l : 0.f;
       uint8_t *stage = smem + L::kQOff + t * L::kTileBytes;  // Q_t is dead: all S MMAs of this tile have completed
       constexpr int kChunks = HD / 8;                        // 16-byte chunks per row
 #pragma unroll
@@ -668,7 +725,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       }
       tc_fence_before();
       if (row < ti.sq)
-        lse_ptr[row] = (l > 0.f) ? (m_ref * p.softmax_scale + __logf(l))
+        lse_ptr[row] = nonempty ? (m_ref * p.softmax_scale + __logf(l))
                                  : (p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F);
       named_bar_sync(1 + t, kBM);
       {
