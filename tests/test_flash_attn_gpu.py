@@ -134,3 +134,25 @@ def test_flash_attn_race_condition(fa):
         assert torch.equal(out, out0) and torch.equal(lse, lse0)
         assert torch.equal(dk, dk0) and torch.equal(dv, dv0)
         assert (dq - dq0).abs().max().item() <= 2 * (dq0.abs().max().item() * 2 ** -7)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_host_pipeline_matches_device_path(fa, causal):
+    """HostPipeline (pinned host in / out, chunked over three streams) == flash_attn_func on the device, bit for bit."""
+    torch.manual_seed(0)
+    b, s, h, hk, d = 5, 640, 4, 2, 128
+    mk = lambda *shape: torch.randn(*shape, dtype=torch.bfloat16).pin_memory()
+    q, k, v, g = mk(b, s, h, d), mk(b, s, hk, d), mk(b, s, hk, d), mk(b, s, h, d)
+    outs = [torch.empty_like(t).pin_memory() for t in (q, q, k, v)]
+    pipe = fa.HostPipeline("cuda", chunk=2, causal=causal)
+    for _ in range(2):   # second run reuses the staging buffers
+        pipe.run(q, k, v, g, *outs)
+    pipe.synchronize()
+    qd, kd, vd = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+    o = fa.flash_attn_func(qd, kd, vd, causal=causal)
+    dq, dk, dv = torch.autograd.grad(o, (qd, kd, vd), g.cuda())
+    assert torch.equal(outs[0], o.detach().cpu())
+    assert torch.equal(outs[2], dk.cpu()) and torch.equal(outs[3], dv.cpu())
+    torch.testing.assert_close(outs[1].float(), dq.cpu().float(), atol=2e-2, rtol=2e-2)   # dQ: fp32 atomics order
+    with pytest.raises(ValueError):
+        pipe.run(q.cuda(), k, v, g, *outs)
