@@ -1,0 +1,210 @@
+"""The setter-style params-handle ABI (include/fa_handle.h; reference csrc/flashmask_v2/flash_api.h:14-266 and
+csrc/flash_attn_v3/flash_api.h).  CPU: every declared symbol is exported and getters return what setters stored.
+GPU: forward / backward / split-KV driven exactly the way Paddle drives the reference (create, set fields, run)."""
+import ctypes as C
+import importlib
+import math
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+from oracle import attention_oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+capi = importlib.import_module("xhy-flash-attention_b200._capi")
+
+
+def _declared():
+    """Expand the X-macros of fa_handle.h with the C preprocessor and collect the function names."""
+    src = subprocess.run(["gcc", "-E", "-P", "-I", os.path.join(ROOT, "include"), "-I", "/usr/local/cuda/include",
+                          os.path.join(ROOT, "include", "fa_handle.h")], capture_output=True, text=True, check=True).stdout
+    return sorted(set(re.findall(r"\b((?:flashmaskv2|fa3)_\w+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(capi.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    return C.CDLL(capi.LIB_PATH)
+
+
+def test_every_handle_symbol_is_exported(lib):
+    names = _declared()
+    # 13 lifecycle/run functions per prefix; 4 accessors per shared field, 2 per backward-only field
+    assert len(names) > 900 and "flashmaskv2_run_mha_fwd" in names and "fa3_bwd_params_set_dq_accum_ptr" in names
+    assert "flashmaskv2_fwd_params_set_lt_start_ptr" in names and "fa3_fwd_params_set_lt_start_ptr" not in names
+    out = subprocess.run(["nm", "-D", "--defined-only", capi.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    exported = {line.split()[-1] for line in out.splitlines() if line.strip()}
+    missing = [n for n in names if n not in exported]
+    assert not missing, missing[:10]
+
+
+def test_setters_and_getters_roundtrip(lib):
+    for prefix in ("flashmaskv2", "fa3"):
+        create = getattr(lib, f"{prefix}_create_bwd_params_handle"); create.restype = C.c_void_p
+        cast = getattr(lib, f"{prefix}_cast_to_fwd_params_handle"); cast.restype = C.c_void_p; cast.argtypes = [C.c_void_p]
+        h = create()
+        assert h
+        for member, ctype, val in (("seqlen_q", C.c_int, 777), ("q_row_stride", C.c_int64, 1 << 40),
+                                   ("scale_softmax", C.c_float, 0.125), ("is_causal", C.c_bool, True),
+                                   ("do_head_stride", C.c_int64, 128)):
+            s = getattr(lib, f"{prefix}_bwd_params_set_{member}"); s.argtypes = [C.c_void_p, ctype]; s.restype = None
+            g = getattr(lib, f"{prefix}_bwd_params_get_{member}"); g.argtypes = [C.c_void_p]; g.restype = ctype
+            s(h, val)
+            assert g(h) == val
+        # the forward view of a backward handle sees the same fields
+        g = getattr(lib, f"{prefix}_fwd_params_get_seqlen_q"); g.argtypes = [C.c_void_p]; g.restype = C.c_int
+        assert g(cast(h)) == 777
+        clear = getattr(lib, f"{prefix}_clear_bwd_params_handle"); clear.argtypes = [C.c_void_p]
+        clear(h)
+        assert g(cast(h)) == 0
+        destroy = getattr(lib, f"{prefix}_destroy_bwd_params_handle"); destroy.argtypes = [C.c_void_p]
+        destroy(h)
+
+
+# ---------------------------------------------------------------------------------------------------- GPU
+_CT = {int: C.c_int, float: C.c_float, bool: C.c_bool}
+
+
+class Handle:
+    def __init__(self, lib, prefix, kind):
+        self.lib, self.prefix, self.kind = lib, prefix, kind
+        f = getattr(lib, f"{prefix}_create_{kind}_params_handle"); f.restype = C.c_void_p
+        self.h = f()
+
+    def set(self, **kw):
+        for k, v in kw.items():
+            f = getattr(self.lib, f"{self.prefix}_{self.kind}_params_set_{k}")
+            if isinstance(v, torch.Tensor):
+                f.argtypes = [C.c_void_p, C.c_void_p]; v = v.data_ptr()
+            elif k.endswith("_stride"):
+                f.argtypes = [C.c_void_p, C.c_int64]
+            else:
+                f.argtypes = [C.c_void_p, _CT[type(v)]]
+            f.restype = None
+            f(self.h, v)
+
+    def call(self, name, *args, restype=None):
+        f = getattr(self.lib, f"{self.prefix}_{name}")
+        f.argtypes = [C.c_void_p] + [C.c_void_p if not isinstance(a, bool) else C.c_bool for a in args]
+        f.restype = restype
+        return f(self.h, *args)
+
+    def close(self):
+        f = getattr(self.lib, f"{self.prefix}_destroy_{self.kind}_params_handle"); f.argtypes = [C.c_void_p]
+        f(self.h)
+
+
+def _set_qkvo(hd, q, k, v, o, packed=False):
+    for name, t in (("q", q), ("k", k), ("v", v), ("o", o)):
+        strides = (0, t.stride(0), t.stride(1)) if packed else (t.stride(0), t.stride(1), t.stride(2))
+        hd.set(**{f"{name}_ptr": t, f"{name}_batch_stride": strides[0], f"{name}_row_stride": strides[1],
+                  f"{name}_head_stride": strides[2]})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prefix,mask", [("flashmaskv2", "doc"), ("flashmaskv2", None), ("fa3", None)])
+def test_handle_fwd_bwd(fa, prefix, mask):
+    from tests._util import check_2x, check_lse, oracle_all
+    lib = capi.load()
+    torch.manual_seed(0)
+    b, s, h, hk, d = 2, 640, 4, 2, 128
+    dev = "cuda"
+    q, g = [torch.randn(b, s, h, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    k, v = [torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    o, dq = torch.empty_like(q), torch.empty_like(q)
+    dk, dv = torch.empty_like(k), torch.empty_like(v)
+    lse = torch.empty(b, h, s, device=dev, dtype=torch.float32)
+    stream = torch.cuda.current_stream().cuda_stream
+    common = dict(b=b, seqlen_q=s, seqlen_k=s, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d), is_bf16=True,
+                  is_causal=True, num_splits=1, arch=100, num_sm=148, softmax_lse_ptr=lse)
+    dense = orc.causal_mask_bottom_right(s, s)
+    keep = []
+    if mask == "doc":
+        lts = orc.document_lt_start([200, 300, 140]).view(1, 1, s).expand(b, 1, s).contiguous().to(dev)
+        ws = torch.empty(8 * b * ((s + 63) // 64 + 3), dtype=torch.int32, device=dev)
+        common.update(lt_start_ptr=lts, h_flashmask=1, h_h_flashmask_ratio=h, flashmask_maxmin_ptr=ws)
+        keep += [lts, ws]
+        dense = dense | orc.flashmask_dense(s, s, lts.cpu())
+    hf = Handle(lib, prefix, "fwd")
+    _set_qkvo(hf, q, k, v, o)
+    hf.set(**common)
+    hf.call("run_mha_fwd", stream)
+    hb = Handle(lib, prefix, "bwd")
+    _set_qkvo(hb, q, k, v, o)
+    hb.set(**common)
+    for name, t in (("do", g), ("dq", dq), ("dk", dk), ("dv", dv)):
+        hb.set(**{f"{name}_ptr": t, f"{name}_batch_stride": t.stride(0), f"{name}_row_stride": t.stride(1),
+                  f"{name}_head_stride": t.stride(2)})
+    hb.call("run_mha_bwd", stream)
+    torch.cuda.synchronize()
+    ref = oracle_all(q, k, v, g, dense.to(dev), lse_empty=float("-inf"))
+    check_2x("out", o, *ref["out"])
+    check_lse(lse, ref["lse"])
+    check_2x("dq", dq, *ref["dq"])
+    check_2x("dk", dk, *ref["dk"])
+    check_2x("dv", dv, *ref["dv"])
+    hf.close(); hb.close()
+
+
+@pytest.mark.gpu
+def test_handle_varlen_lse_is_packed(fa):
+    from tests._util import check_2x
+    lib = capi.load()
+    torch.manual_seed(1)
+    lens = [100, 333, 64]
+    total, h, d = sum(lens), 4, 128
+    dev = "cuda"
+    q, k, v = [torch.randn(total, h, d, device=dev, dtype=torch.bfloat16) for _ in range(3)]
+    o = torch.empty_like(q)
+    cu = torch.tensor([0, 100, 433, 497], device=dev, dtype=torch.int32)
+    lse = torch.full((h, total), float("nan"), device=dev, dtype=torch.float32)
+    hf = Handle(lib, "flashmaskv2", "fwd")
+    _set_qkvo(hf, q, k, v, o, packed=True)
+    hf.set(b=3, seqlen_q=max(lens), seqlen_k=max(lens), total_q=total, total_k=total, h=h, h_k=h, d=d, dv=d,
+           scale_softmax=1.0 / math.sqrt(d), is_bf16=True, is_causal=True, num_splits=1, softmax_lse_ptr=lse,
+           cu_seqlens_q=cu, cu_seqlens_k=cu)
+    hf.call("run_mha_fwd", torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ref, lses = orc.attention_varlen_ref(q, k, v, cu.tolist(), cu.tolist(), causal=True)
+    pt, _ = orc.attention_varlen_ref(q, k, v, cu.tolist(), cu.tolist(), causal=True, upcast=False, reorder_ops=True)
+    check_2x("out", o, ref, pt)
+    torch.testing.assert_close(lse, torch.cat(lses, dim=1), atol=2e-3, rtol=1e-3)   # (h, total_q)
+    hf.close()
+
+
+@pytest.mark.gpu
+def test_handle_decode_split_and_combine(fa):
+    from tests._util import check_2x
+    lib = capi.load()
+    torch.manual_seed(2)
+    b, sk, h, hk, d, splits = 3, 2000, 8, 2, 128, 4
+    dev = "cuda"
+    q = torch.randn(b, 1, h, d, device=dev, dtype=torch.bfloat16)
+    kc, vc = [torch.randn(b, sk, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    o = torch.empty_like(q)
+    lse = torch.empty(b, h, 1, device=dev, dtype=torch.float32)
+    used = torch.tensor([2000, 1234, 77], device=dev, dtype=torch.int32)
+    oacc = torch.empty(splits, b, 1, h, d, device=dev, dtype=torch.float32)
+    lacc = torch.empty(splits, b, h, 1, device=dev, dtype=torch.float32)
+    hf = Handle(lib, "fa3", "fwd")
+    _set_qkvo(hf, q, kc, vc, o)
+    hf.set(b=b, seqlen_q=1, seqlen_k=sk, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d), is_bf16=True,
+           is_causal=True, seqused_k=used, softmax_lse_ptr=lse, num_sm=148)
+    assert hf.call("get_pack_gqa", restype=C.c_bool)
+    assert hf.call("get_num_splits", restype=C.c_int) >= 1
+    hf.set(num_splits=splits, oaccum_ptr=oacc, softmax_lseaccum_ptr=lacc)
+    stream = torch.cuda.current_stream().cuda_stream
+    hf.call("run_mha_fwd", stream)
+    hf.call("run_mha_fwd_combine", stream, False)
+    torch.cuda.synchronize()
+    for i in range(b):
+        n = int(used[i])
+        ref, _ = orc.attention_masked_ref(q[i:i + 1], kc[i:i + 1, :n], vc[i:i + 1, :n])
+        pt, _ = orc.attention_masked_ref(q[i:i + 1], kc[i:i + 1, :n], vc[i:i + 1, :n], upcast=False, reorder_ops=True)
+        check_2x("out", o[i:i + 1], ref, pt)
+    hf.close()

@@ -1,0 +1,241 @@
+// handle_abi.cu -- the setter-style params handles of the reference's FlashMask-v2 / FA3 libraries (include/fa_handle.h).
+//
+// Replaces csrc/flashmask_v2/flash_api.{h,cu} and csrc/flash_attn_v3/flash_api.{h,cu}: the handle is a heap object with
+// one slot per field of the reference's Flash_fwd_params / Flash_bwd_params (csrc/flashmask_v2/flash.h:13-231); the run
+// functions translate the slots into fa_b200_params and take the same dispatchers as every other entry point.
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "common.h"
+#include "../../include/fa_handle.h"
+
+#define FA_SLOT(type, member) type member;
+struct Flash_fwd_params {
+  FA_HANDLE_FWD_FIELDS(FA_SLOT)
+  FA_HANDLE_MASK_FIELDS(FA_SLOT)
+};
+struct Flash_bwd_params : public Flash_fwd_params {
+  FA_HANDLE_BWD_FIELDS(FA_SLOT)
+  FA_HANDLE_BWD_MASK_FIELDS(FA_SLOT)
+};
+#undef FA_SLOT
+
+namespace {
+
+using fa::Params;
+
+void require(bool ok, const char *what) {
+  if (!ok) throw fa::Error(std::string("params handle: ") + what);
+}
+
+fa_b200_tensor tens(void *ptr, int64_t bs, int64_t rs, int64_t hs) {
+  fa_b200_tensor t;
+  t.ptr = ptr; t.batch_stride = bs; t.row_stride = rs; t.head_stride = hs;
+  return t;
+}
+
+bool decode_shape(const Flash_fwd_params &h) {
+  return h.cu_seqlens_q == nullptr && h.cu_seqlens_k == nullptr && h.lt_start_ptr == nullptr && h.h_k > 0 &&
+         h.seqlen_q * (h.h / h.h_k) <= 16 && (h.d == 64 || h.d == 128);
+}
+
+// (h, total_q) <-> (b, h, max_seqlen_q): the v2/v3 surface keeps varlen LSE packed (flash_fwd_launch_template.h:161-164)
+__global__ void lse_repack_kernel(float *packed, float *padded, const int *cu, int b, int h, int max_sq, int64_t total_q,
+                                  int to_packed) {
+  const int bi = blockIdx.z, hq = blockIdx.y;
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r0 = cu[bi], n = cu[bi + 1] - r0;
+  if (row >= n) return;
+  float *a = packed + (int64_t)hq * total_q + r0 + row;
+  float *c = padded + ((int64_t)bi * h + hq) * max_sq + row;
+  if (to_packed) *a = *c; else *c = *a;
+}
+
+Params common_params(const Flash_fwd_params &h) {
+  require(!h.is_e4m3 && !h.is_fp32, "only fp16 / bf16 inputs are supported");
+  require(h.softcap == 0.f, "softcap is not supported");
+  require(h.page_table == nullptr, "paged KV is not supported");
+  require(h.rotary_cos_ptr == nullptr && h.rotary_sin_ptr == nullptr, "rotary embedding is not supported");
+  require(h.qv_ptr == nullptr, "qv is not supported");
+  require(h.kv_batch_idx == nullptr && h.leftpad_k == nullptr && h.seqused_q == nullptr,
+          "kv_batch_idx / leftpad_k / seqused_q are not supported");
+  require(h.knew_ptr == nullptr && h.vnew_ptr == nullptr, "knew / vnew: append with fa_b200_append_kv before the call");
+  require(h.p_dropout == 0.f || h.p_dropout >= 1.f, "dropout is not supported (p_dropout is the keep probability)");
+  require(h.dv == 0 || h.dv == h.d, "dv != d is not supported");
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.abi_version = FA_B200_ABI_VERSION;
+  p.is_bf16 = h.is_bf16 ? 1 : 0;
+  p.q = tens(h.q_ptr, h.q_batch_stride, h.q_row_stride, h.q_head_stride);
+  p.k = tens(h.k_ptr, h.k_batch_stride, h.k_row_stride, h.k_head_stride);
+  p.v = tens(h.v_ptr, h.v_batch_stride, h.v_row_stride, h.v_head_stride);
+  p.o = tens(h.o_ptr, h.o_batch_stride, h.o_row_stride, h.o_head_stride);
+  p.b = h.b; p.seqlen_q = h.seqlen_q; p.seqlen_k = h.seqlen_k; p.h = h.h; p.h_k = h.h_k; p.d = h.d;
+  p.seqlen_q_rounded = fa::round_up(h.seqlen_q, 128); p.seqlen_k_rounded = fa::round_up(h.seqlen_k, 128);
+  p.d_rounded = fa::round_up(h.d, 32);
+  p.total_q = h.cu_seqlens_q ? h.total_q : -1;
+  p.total_k = h.cu_seqlens_k ? h.total_k : -1;
+  p.cu_seqlens_q = h.cu_seqlens_q; p.cu_seqlens_k = h.cu_seqlens_k; p.seqused_k = h.seqused_k;
+  p.softmax_scale = h.scale_softmax;
+  p.lse_empty_is_neg_inf = 1;                          // csrc/flashmask_v2/softmax.h:153
+  p.is_causal = h.is_causal ? 1 : 0;
+  p.causal_bottom_right = 1;                           // csrc/flashmask_v2/mask.h:85-97
+  p.window_left = h.is_local ? h.window_size_left : -1;
+  p.window_right = h.is_local ? h.window_size_right : -1;
+  if (h.lt_start_ptr) {
+    p.lt_start = h.lt_start_ptr; p.lt_end = h.lt_end_ptr; p.ut_start = h.ut_start_ptr; p.ut_end = h.ut_end_ptr;
+    p.h_mask = h.h_flashmask > 0 ? h.h_flashmask : 1;
+    p.flashmask_maxmin = h.flashmask_maxmin_ptr;
+  }
+  return p;
+}
+
+void set_split(Params &p, const Flash_fwd_params &h) {
+  p.num_splits = h.num_splits;
+  if (h.num_splits > 1) {
+    require(h.oaccum_ptr && h.softmax_lseaccum_ptr, "split-KV needs oaccum_ptr and softmax_lseaccum_ptr");
+    const int64_t hd = (int64_t)h.h * h.d, rows = (int64_t)h.seqlen_q;
+    require((h.oaccum_head_stride == 0 || h.oaccum_head_stride == h.d) && (h.oaccum_row_stride == 0 || h.oaccum_row_stride == hd) &&
+            (h.oaccum_batch_stride == 0 || h.oaccum_batch_stride == rows * hd) &&
+            (h.oaccum_split_stride == 0 || h.oaccum_split_stride == (int64_t)h.b * rows * hd),
+            "oaccum must be contiguous (splits, b, seqlen_q, h, d)");
+    require((h.lseaccum_head_stride == 0 || h.lseaccum_head_stride == rows) &&
+            (h.lseaccum_batch_stride == 0 || h.lseaccum_batch_stride == (int64_t)h.h * rows) &&
+            (h.lseaccum_split_stride == 0 || h.lseaccum_split_stride == (int64_t)h.b * h.h * rows),
+            "softmax_lseaccum must be contiguous (splits, b, h, seqlen_q)");
+    p.oaccum = (float *)h.oaccum_ptr; p.lseaccum = (float *)h.softmax_lseaccum_ptr;
+  }
+}
+
+void run_fwd_handle(Flash_fwd_params *hp, cudaStream_t stream) {
+  require(hp != nullptr, "null handle");
+  const Flash_fwd_params &h = *hp;
+  Params p = common_params(h);
+  require(h.softmax_lse_ptr != nullptr, "softmax_lse_ptr must be set");
+  set_split(p, h);
+  if (h.num_splits > 1 || decode_shape(h)) {
+    p.softmax_lse = (float *)h.softmax_lse_ptr;
+    fa::run_splitkv(p, stream);
+    return;
+  }
+  if (h.cu_seqlens_q) {   // varlen: the kernels write (b, h, max_seqlen_q); this surface wants (h, total_q)
+    require(h.total_q > 0, "total_q must be set with cu_seqlens_q");
+    float *tmp = nullptr;
+    FA_CUDA(cudaMallocAsync(&tmp, sizeof(float) * (size_t)h.b * h.h * h.seqlen_q, stream));
+    p.softmax_lse = tmp;
+    fa::run_fwd(p, stream);
+    dim3 grid(fa::ceil_div(h.seqlen_q, 128), h.h, h.b);
+    lse_repack_kernel<<<grid, 128, 0, stream>>>((float *)h.softmax_lse_ptr, tmp, h.cu_seqlens_q, h.b, h.h, h.seqlen_q,
+                                                h.total_q, 1);
+    FA_CUDA(cudaGetLastError());
+    FA_CUDA(cudaFreeAsync(tmp, stream));
+    return;
+  }
+  p.softmax_lse = (float *)h.softmax_lse_ptr;
+  fa::run_fwd(p, stream);
+}
+
+void run_combine_handle(Flash_fwd_params *hp, cudaStream_t stream) {
+  require(hp != nullptr, "null handle");
+  const Flash_fwd_params &h = *hp;
+  Params p = common_params(h);
+  require(h.num_splits > 1, "run_mha_fwd_combine needs num_splits > 1");
+  set_split(p, h);
+  p.softmax_lse = (float *)h.softmax_lse_ptr;
+  require(p.softmax_lse && p.o.ptr, "o_ptr and softmax_lse_ptr must be set");
+  fa::combine_fwd(p, stream);
+}
+
+void run_bwd_handle(Flash_bwd_params *hp, cudaStream_t stream) {
+  require(hp != nullptr, "null handle");
+  const Flash_bwd_params &h = *hp;
+  Params p = common_params(h);
+  require(h.do_ptr && h.dq_ptr && h.dk_ptr && h.dv_ptr && h.softmax_lse_ptr, "do / dq / dk / dv / softmax_lse must be set");
+  p.dout = tens(h.do_ptr, h.do_batch_stride, h.do_row_stride, h.do_head_stride);
+  p.dq = tens(h.dq_ptr, h.dq_batch_stride, h.dq_row_stride, h.dq_head_stride);
+  p.dk = tens(h.dk_ptr, h.dk_batch_stride, h.dk_row_stride, h.dk_head_stride);
+  p.dv = tens(h.dv_ptr, h.dv_batch_stride, h.dv_row_stride, h.dv_head_stride);
+  p.dkv_expanded = 0;                      // dk / dv carry h_k heads; the group is reduced inside the kernel
+  p.deterministic = h.deterministic ? 1 : 0;
+  // Workspaces: the caller's dq_accum / dsoftmax_sum / softmax_lse_log2 are sized for the reference's sm90 tile shapes
+  // (flash_bwd_launch_template.h:42-49), not for the 128-row tiles used here, so this path takes stream-ordered
+  // scratch of its own size instead.
+  const bool varlen = h.cu_seqlens_q != nullptr;
+  if (varlen) require(h.total_q > 0, "total_q must be set with cu_seqlens_q");
+  const size_t acc_rows = varlen ? (size_t)h.h * fa::round_up((int)(h.total_q + 128 * (int64_t)h.b), 128)
+                                 : (size_t)h.b * h.h * p.seqlen_q_rounded;
+  const size_t n_acc = acc_rows * p.d_rounded, n_d = (size_t)h.b * h.h * p.seqlen_q_rounded;
+  const size_t n_lse = varlen ? (size_t)h.b * h.h * h.seqlen_q : 0;
+  float *scratch = nullptr;
+  FA_CUDA(cudaMallocAsync(&scratch, sizeof(float) * (n_acc + n_d + n_lse), stream));
+  p.dq_accum = scratch; p.softmax_d = scratch + n_acc;
+  if (varlen) {
+    float *tmp = scratch + n_acc + n_d;
+    dim3 grid(fa::ceil_div(h.seqlen_q, 128), h.h, h.b);
+    lse_repack_kernel<<<grid, 128, 0, stream>>>((float *)h.softmax_lse_ptr, tmp, h.cu_seqlens_q, h.b, h.h, h.seqlen_q,
+                                                h.total_q, 0);
+    FA_CUDA(cudaGetLastError());
+    p.softmax_lse = tmp;
+  } else {
+    p.softmax_lse = (float *)h.softmax_lse_ptr;
+  }
+  try {
+    fa::run_bwd(p, stream);
+  } catch (...) {
+    cudaFreeAsync(scratch, stream);
+    throw;
+  }
+  FA_CUDA(cudaFreeAsync(scratch, stream));
+}
+
+int num_splits_handle(const Flash_fwd_params &h) {
+  const int num_sm = h.num_sm > 0 ? h.num_sm : fa::device_sm_count();
+  if (h.h_k <= 0) return 1;
+  if (decode_shape(h)) return fa_b200_decode_num_splits(h.b, h.h_k, h.seqlen_k, num_sm);
+  return fa_b200_num_splits(h.b, h.h_k, h.seqlen_q * (h.h / h.h_k), h.seqlen_k, h.d, num_sm);
+}
+
+}  // namespace
+
+extern "C" {
+
+#define FA_HANDLE_LIFECYCLE(P)                                                                                       \
+  Flash_fwd_params *P##_create_fwd_params_handle(void) { return new (std::nothrow) Flash_fwd_params(); }             \
+  Flash_bwd_params *P##_create_bwd_params_handle(void) { return new (std::nothrow) Flash_bwd_params(); }             \
+  void P##_clear_fwd_params_handle(Flash_fwd_params *h) { if (h) *h = Flash_fwd_params(); }                          \
+  void P##_clear_bwd_params_handle(Flash_bwd_params *h) { if (h) *h = Flash_bwd_params(); }                          \
+  Flash_fwd_params *P##_cast_to_fwd_params_handle(Flash_bwd_params *h) { return static_cast<Flash_fwd_params *>(h); } \
+  void P##_destroy_fwd_params_handle(Flash_fwd_params *h) { delete h; }                                              \
+  void P##_destroy_bwd_params_handle(Flash_bwd_params *h) { delete h; }                                              \
+  void P##_run_mha_fwd_combine(Flash_fwd_params *h, cudaStream_t s, bool) { run_combine_handle(h, s); }              \
+  void P##_run_mha_fwd(Flash_fwd_params *h, cudaStream_t s) { run_fwd_handle(h, s); }                                \
+  bool P##_get_pagedkv_tma(Flash_fwd_params *) { return false; }                                                     \
+  bool P##_get_pack_gqa(Flash_fwd_params *h) { return h && decode_shape(*h); }                                       \
+  int P##_get_num_splits(Flash_fwd_params *h) { return h ? num_splits_handle(*h) : 1; }                              \
+  void P##_run_mha_bwd(Flash_bwd_params *h, cudaStream_t s) { run_bwd_handle(h, s); }
+
+FA_HANDLE_LIFECYCLE(flashmaskv2)
+FA_HANDLE_LIFECYCLE(fa3)
+
+#define FA_DEF_BOTH(P, type, member)                                                                      \
+  type P##_fwd_params_get_##member(const Flash_fwd_params *h) { return h->member; }                       \
+  void P##_fwd_params_set_##member(Flash_fwd_params *h, type value) { h->member = value; }          \
+  type P##_bwd_params_get_##member(const Flash_bwd_params *h) { return h->member; }                       \
+  void P##_bwd_params_set_##member(Flash_bwd_params *h, type value) { h->member = value; }
+#define FA_DEF_BWD(P, type, member)                                                                       \
+  type P##_bwd_params_get_##member(const Flash_bwd_params *h) { return h->member; }                       \
+  void P##_bwd_params_set_##member(Flash_bwd_params *h, type value) { h->member = value; }
+#define FA_DEF_BOTH_V2(type, member) FA_DEF_BOTH(flashmaskv2, type, member)
+#define FA_DEF_BWD_V2(type, member) FA_DEF_BWD(flashmaskv2, type, member)
+#define FA_DEF_BOTH_FA3(type, member) FA_DEF_BOTH(fa3, type, member)
+#define FA_DEF_BWD_FA3(type, member) FA_DEF_BWD(fa3, type, member)
+
+FA_HANDLE_FWD_FIELDS(FA_DEF_BOTH_V2)
+FA_HANDLE_MASK_FIELDS(FA_DEF_BOTH_V2)
+FA_HANDLE_BWD_FIELDS(FA_DEF_BWD_V2)
+FA_HANDLE_BWD_MASK_FIELDS(FA_DEF_BWD_V2)
+FA_HANDLE_FWD_FIELDS(FA_DEF_BOTH_FA3)
+FA_HANDLE_BWD_FIELDS(FA_DEF_BWD_FA3)
+
+}  // extern "C"
