@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 1
+#define FA_B200_ABI_VERSION 2
 
 /* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
  * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
@@ -79,6 +79,12 @@ typedef struct fa_b200_params {
   int32_t num_splits;             /* 0/1 = no split */
   float  *oaccum;                 /* (num_splits, b, seqlen_q, h, d) fp32 */
   float  *lseaccum;               /* (num_splits, b, h, seqlen_q) fp32 */
+
+  /* ---- dropout (ABI v2; reference: csrc/flash_attn/src/flash.h:88-94, softmax.h:381-447) ---- */
+  float    p_dropout;             /* probability of DROPPING an attention weight; 0 = off */
+  uint64_t philox_seed, philox_offset; /* keep iff philox_byte(seed, offset, b, h, row, col) <= floor(255 * (1 - p)) */
+  void    *s_dmask;               /* optional (b, h, seqlen_q_rounded, seqlen_k_rounded) in the element type: softmax
+                                     probabilities, NEGATED where the weight was dropped (return_softmax), or NULL */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

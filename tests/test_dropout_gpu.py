@@ -1,0 +1,88 @@
+"""GPU parity for dropout and return_attn_probs, the way the reference's tests do it (tests/test_flash_attn.py:
+376-427): take the dropout mask the kernel actually used from S_dmask, give the SAME mask to the fp32 oracle
+``attention_ref``, compare out / dq / dk / dv with the 2x criterion, check the normalised probabilities and that the
+dropped fraction is within 0.01 of dropout_p."""
+import math
+
+import pytest
+import torch
+
+from oracle import attention_oracle as orc
+from tests._util import check_2x
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _ref_with_mask(q, k, v, g, keep, causal, p, upcast=True, reorder_ops=False):
+    q_, k_, v_ = [t.detach().clone().requires_grad_(True) for t in (q, k, v)]
+    out, attn = orc.attention_ref(q_, k_, v_, None, None, p, keep, causal=causal, upcast=upcast, reorder_ops=reorder_ops)
+    dq, dk, dv = torch.autograd.grad(out, (q_, k_, v_), g.to(out.dtype))
+    return out.detach(), attn.detach(), dq, dk, dv
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("h,hk", [(4, 4), (6, 2)])
+@pytest.mark.parametrize("sq,sk,d", [(128, 128, 64), (113, 203, 128), (256, 512, 32)])
+def test_dropout_output_and_grads(fa, sq, sk, d, h, hk, causal, dtype):
+    torch.manual_seed(0)
+    b, p = 3, 0.17
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=dtype, requires_grad=True)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=dtype)
+    out, lse, S = fa.flash_attn_func(q, k, v, p, None, causal, True)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    assert S.shape == (b, h, (sq + 127) // 128 * 128, (sk + 127) // 128 * 128)
+    S = S[:, :, :sq, :sk].float()
+    keep = S >= 0                                   # dropped weights are stored negated
+    ref = _ref_with_mask(q, k, v, g, keep, causal, p)
+    pt = _ref_with_mask(q, k, v, g, keep, causal, p, upcast=False, reorder_ops=True)
+    check_2x("out", out, ref[0], pt[0])
+    check_2x("dq", dq, ref[2], pt[2])
+    check_2x("dk", dk, ref[3], pt[3])
+    check_2x("dv", dv, ref[4], pt[4])
+    # the probabilities themselves (reference: attn vs attn_ref, :420-421)
+    attn = S.abs()
+    assert (attn - ref[1].float()).abs().max().item() <= 2 * (pt[1].float() - ref[1].float()).abs().max().item() + 1e-3
+    # dropped fraction over the visible entries (reference: :422-424, tolerance 0.01)
+    vis = torch.ones(sq, sk, dtype=torch.bool, device=DEV) if not causal else ~orc.causal_mask_top_left(sq, sk).to(DEV)
+    frac = (~keep)[:, :, vis].float().mean().item()
+    assert abs(frac - p) < 0.01, frac
+    # LSE is independent of dropout
+    _, lse0, _ = fa.flash_attn_func(q, k, v, 0.0, None, causal, True)
+    torch.testing.assert_close(lse, lse0, atol=2e-3, rtol=1e-3)
+
+
+def test_dropout_is_reproducible_and_seeded(fa):
+    b, s, h, d = 2, 256, 4, 64
+    q, k, v = [torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    torch.manual_seed(7)
+    a1 = fa.flash_attn_func(q, k, v, 0.3)
+    torch.manual_seed(7)
+    a2 = fa.flash_attn_func(q, k, v, 0.3)
+    a3 = fa.flash_attn_func(q, k, v, 0.3)
+    assert torch.equal(a1, a2) and not torch.equal(a1, a3)
+    with pytest.raises(ValueError):
+        fa.flash_attn_func(q, k, v, 1.0)
+
+
+def test_dropout_varlen_and_packed(fa):
+    torch.manual_seed(3)
+    lens, h, d, p = [77, 200, 130], 4, 64, 0.25
+    total = sum(lens)
+    qkv = torch.randn(total, 3, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    cu = torch.tensor([0, 77, 277, 407], device=DEV, dtype=torch.int32)
+    out, lse, S = fa.flash_attn_varlen_qkvpacked_func(qkv, cu, max(lens), p, None, True, True)
+    g = torch.randn_like(out)
+    (dqkv,) = torch.autograd.grad(out, qkv, g)
+    for i, n in enumerate(lens):
+        a, e = int(cu[i]), int(cu[i + 1])
+        keep = S[i:i + 1, :, :n, :n] >= 0
+        q, k, v = [qkv[a:e, j].unsqueeze(0) for j in range(3)]
+        ref = _ref_with_mask(q, k, v, g[a:e].unsqueeze(0), keep, True, p)
+        pt = _ref_with_mask(q, k, v, g[a:e].unsqueeze(0), keep, True, p, upcast=False, reorder_ops=True)
+        check_2x("out", out[a:e].unsqueeze(0), ref[0], pt[0])
+        for j, name in enumerate(("dq", "dk", "dv")):
+            check_2x(name, dqkv[a:e, j].unsqueeze(0), ref[2 + j], pt[2 + j])

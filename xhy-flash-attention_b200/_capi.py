@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
 LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
-FA_B200_ABI_VERSION = 1
+FA_B200_ABI_VERSION = 2
 
 
 class Tensor(C.Structure):
@@ -45,6 +45,7 @@ class Params(C.Structure):
         ("h_mask", C.c_int32), ("flashmask_maxmin", C.c_void_p),
         ("dkv_expanded", C.c_int32), ("deterministic", C.c_int32), ("force_generic", C.c_int32),
         ("num_splits", C.c_int32), ("oaccum", C.c_void_p), ("lseaccum", C.c_void_p),
+        ("p_dropout", C.c_float), ("philox_seed", C.c_uint64), ("philox_offset", C.c_uint64), ("s_dmask", C.c_void_p),
     ]
 
 

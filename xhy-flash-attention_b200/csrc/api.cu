@@ -72,7 +72,10 @@ void run_fwd(const Params &p, cudaStream_t s) {
   check_common(p);
   FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
   std::string why;
-  if (!p.force_generic && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
+  FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
+  // dropout / return_softmax take the generic kernels (Philox per element); the tcgen05 kernels are dropout-free
+  const bool special = p.p_dropout > 0.f || p.s_dmask != nullptr;
+  if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
   else generic_fwd(p, s);
 }
 
@@ -81,7 +84,8 @@ void run_bwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.o.ptr && p.softmax_lse && p.dout.ptr && p.dq.ptr && p.dk.ptr && p.dv.ptr, "bwd tensors must be set");
   FA_CHECK(p.softmax_d, "softmax_d workspace must be set");
   std::string why;
-  if (!p.force_generic && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
+  FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
+  if (!p.force_generic && !(p.p_dropout > 0.f) && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }
 

@@ -89,11 +89,14 @@ bool flash_attn_fwd(
     int v_row_stride, int q_head_stride, int k_head_stride, int v_head_stride, int o_row_stride, int o_head_stride,
     int q_batch_stride, int k_batch_stride, int v_batch_stride, int o_batch_stride) {
   FA_BEGIN
-  unsupported(p_dropout > 0.f, "dropout");
-  unsupported(return_softmax, "return_softmax");
   unsupported(attn_mask != nullptr, "dense attn_mask");
   Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
                          head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;   // csrc/capi/flash_attn.cu:672-677
+  if (return_softmax) {
+    FA_CHECK(softmax_ptr != nullptr, "return_softmax needs softmax_ptr");
+    p.s_dmask = softmax_ptr;
+  }
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
   p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
@@ -120,12 +123,15 @@ bool flash_attn_varlen_fwd(
     int v_head_stride, int o_row_stride, int o_head_stride, int q_batch_stride, int k_batch_stride, int v_batch_stride,
     int o_batch_stride, bool varlen_padded_input) {
   FA_BEGIN
-  unsupported(p_dropout > 0.f, "dropout");
-  unsupported(return_softmax, "return_softmax");
   unsupported(attn_mask != nullptr, "dense attn_mask");
   FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
   Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
                          num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
+  if (return_softmax) {
+    FA_CHECK(softmax_ptr != nullptr, "return_softmax needs softmax_ptr");
+    p.s_dmask = softmax_ptr;
+  }
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
   p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
@@ -156,10 +162,10 @@ bool flash_attn_bwd(
     int dq_head_stride, int dk_head_stride, int dv_head_stride, int do_row_stride, int do_head_stride,
     int dq_batch_stride, int dk_batch_stride, int dv_batch_stride, int do_batch_stride) {
   FA_BEGIN
-  unsupported(p_dropout > 0.f, "dropout");
   unsupported(attn_mask != nullptr, "dense attn_mask");
   Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
                          head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
   p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);
@@ -193,11 +199,11 @@ bool flash_attn_varlen_bwd(
     int dv_head_stride, int do_row_stride, int do_head_stride, int dq_batch_stride, int dk_batch_stride,
     int dv_batch_stride, int do_batch_stride, bool varlen_padded_input) {
   FA_BEGIN
-  unsupported(p_dropout > 0.f, "dropout");
   unsupported(attn_mask != nullptr, "dense attn_mask");
   FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
   Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
                          num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
   p.v = tensor(v, v_batch_stride, v_row_stride, v_head_stride);

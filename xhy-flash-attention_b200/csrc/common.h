@@ -86,6 +86,39 @@ __host__ __device__ inline bool flashmask_has_l2(int seqlen_k, int block_n) {
 }
 
 #ifdef __CUDACC__
+// Philox-4x32-10 (Salmon et al., SC'11; the generator behind csrc/flash_attn/src/philox.cuh): key = seed,
+// counter = (offset, subsequence).  One call yields 16 random bytes.
+__device__ __forceinline__ uint4 philox4x32_10(uint64_t seed, uint64_t subsequence, uint64_t offset) {
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  uint4 c = make_uint4((uint32_t)offset, (uint32_t)(offset >> 32), (uint32_t)subsequence, (uint32_t)(subsequence >> 32));
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return c;
+}
+// Dropout decision for attention weight (b, h, row, col): 16 consecutive columns share one Philox call; the weight is
+// KEPT iff its byte <= floor(255 * p_keep) -- the reference's 8-bit threshold (flash.h:88-94, softmax.h:392-436).
+struct DropCtx {
+  uint64_t seed, offset, row_base;   // row_base = ((b * h + head) * seqlen_q + row) * ceil(seqlen_k / 16)
+  uint32_t threshold;
+};
+__device__ __forceinline__ bool dropout_keep(const DropCtx &d, int col) {
+  const uint4 r = philox4x32_10(d.seed, d.row_base + (uint32_t)(col >> 4), d.offset);
+  const uint32_t w = ((col >> 2) & 3) == 0 ? r.x : ((col >> 2) & 3) == 1 ? r.y : ((col >> 2) & 3) == 2 ? r.z : r.w;
+  return ((w >> ((col & 3) * 8)) & 0xffu) <= d.threshold;
+}
+__device__ __forceinline__ DropCtx make_drop_ctx(const Params &p, int bi, int head, int row) {
+  DropCtx d;
+  d.seed = p.philox_seed; d.offset = p.philox_offset;
+  d.row_base = (((uint64_t)bi * p.h + head) * (uint64_t)p.seqlen_q + row) * (uint64_t)((p.seqlen_k + 15) / 16);
+  d.threshold = (uint32_t)floorf((1.f - p.p_dropout) * 255.f);
+  return d;
+}
+
 // Restates csrc/flash_attn/src/block_info.h:12-37 (sum_s = cu_seqlens[b], actual = cu[b+1]-cu[b];
 // varlen_padded_input keeps the batch stride) plus seqused_k of csrc/flashmask_v2/seqlen.h:56-91.
 __device__ __forceinline__ void seq_bounds(const Params &p, int bi, int &q_row0, int &sq, int &k_row0, int &sk,

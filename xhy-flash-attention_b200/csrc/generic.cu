@@ -121,6 +121,9 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
   float o[kMaxC];
 #pragma unroll
   for (int c = 0; c < kMaxC; ++c) o[c] = 0.f;
+  const bool drop = p.p_dropout > 0.f;
+  const DropCtx dc = make_drop_ctx(p, bi, hq, row);
+  const float rp = drop ? 1.f / (1.f - p.p_dropout) : 1.f;
 
   const T *kbase = (const T *)p.k.ptr + elem_off(p.k, sq_.k_boff, sq_.k_row0, hk);
   const T *vbase = (const T *)p.v.ptr + elem_off(p.v, sq_.k_boff, sq_.k_row0, hk);
@@ -132,8 +135,9 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
     const float mnew = fmaxf(mx, warp_max(s));
     if (mnew == -CUDART_INF_F) continue;  // nothing visible so far (warp-uniform)
     const float corr = exp2f(mx - mnew);  // mx = -inf -> 0
-    const float pj = exp2f(s - mnew);     // s = -inf -> 0
-    l = l * corr + warp_sum(pj);
+    float pj = exp2f(s - mnew);           // s = -inf -> 0
+    l = l * corr + warp_sum(pj);          // the row sum is taken BEFORE dropout (flash_fwd_kernel.h:399-409)
+    if (drop && col < hi && !dropout_keep(dc, col)) pj = 0.f;
     mx = mnew;
 #pragma unroll
     for (int c = 0; c < kMaxC; ++c) o[c] *= corr;
@@ -151,7 +155,22 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
   }
 
   const bool empty = !(l > 0.f);
-  const float inv = empty ? 0.f : 1.f / l;
+  const float inv = empty ? 0.f : rp / l;
+  if (!Split && p.s_dmask != nullptr) {
+    // return_softmax: the normalised probabilities, negated where dropped (plain row-major (b, h, sq_r, sk_r); the
+    // reference stores them in its MMA fragment order and de-swizzles in the test, tests/test_flash_attn.py:218-264)
+    T *sd = (T *)p.s_dmask + (((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row) * (int64_t)p.seqlen_k_rounded;
+    const float lse2 = mx + log2f(l);
+    for (int j0 = 0; j0 < p.seqlen_k_rounded; j0 += 32) {
+      const int col = j0 + lane;
+      float pr = 0.f;
+      if (!empty && col >= lo && col < hi && !is_masked(m, row, col)) {
+        pr = exp2f(dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) * scale_log2 - lse2);
+        if (drop && !dropout_keep(dc, col)) pr = -pr;
+      }
+      if (col < p.seqlen_k_rounded) sd[col] = from_f<T>(pr);
+    }
+  }
   if (Split) {
     // partials: oaccum (splits, b, sq, h, d) fp32; lseaccum (splits, b, h, sq) fp32, -inf for an empty split
     float *oa = p.oaccum + ((((int64_t)split * p.b + bi) * p.seqlen_q + row) * p.h + hq) * (int64_t)d;
@@ -218,6 +237,9 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
   const float dsum = p.softmax_d[((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row];
   const bool dead = isinf(lse);
   const float lse2 = dead ? 0.f : lse * kLog2e;
+  const bool drop = p.p_dropout > 0.f;
+  const DropCtx dc = make_drop_ctx(p, bi, hq, row);
+  const float rp = drop ? 1.f / (1.f - p.p_dropout) : 1.f;
   int lo, hi;
   col_range(p, m, row, 0, lo, hi);
   float acc[kMaxC];
@@ -231,7 +253,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
     if (col < hi && !is_masked(m, row, col)) {
       const float sc = dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) * scale_log2;
       const float pij = exp2f(sc - lse2);
-      const float dp = dot_row(g_s[warp], vbase + (int64_t)col * p.v.row_stride, d);
+      float dp = dot_row(g_s[warp], vbase + (int64_t)col * p.v.row_stride, d);
+      if (drop) dp = dropout_keep(dc, col) ? dp * rp : 0.f;   // dP = keep / p_keep * (dO . V)
       ds = pij * (dp - dsum);
     }
     const int nj = min(32, hi - j0);
@@ -277,6 +300,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
   float dk[kMaxC], dv[kMaxC];
 #pragma unroll
   for (int c = 0; c < kMaxC; ++c) { dk[c] = 0.f; dv[c] = 0.f; }
+  const bool drop = p.p_dropout > 0.f;
+  const float rp = drop ? 1.f / (1.f - p.p_dropout) : 1.f;
   for (int hq = hq0; hq < hq1; ++hq) {
     const MaskCtx m = make_mask_ctx(p, bi, hq, s_.sq, s_.sk);
     int rlo = 0, rhi = s_.sq;
@@ -295,8 +320,15 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
         if (!isinf(l)) {
           const float sc = dot_row(k_s[warp], qbase + (int64_t)row * p.q.row_stride, d) * scale_log2;
           pij = exp2f(sc - l * kLog2e);
-          const float dp = dot_row(v_s[warp], gbase + (int64_t)row * p.dout.row_stride, d);
+          float dp = dot_row(v_s[warp], gbase + (int64_t)row * p.dout.row_stride, d);
+          float pd = pij;                                  // the weight dV sees: keep / p_keep * P
+          if (drop) {
+            const bool keep = dropout_keep(make_drop_ctx(p, bi, hq, row), col);
+            dp = keep ? dp * rp : 0.f;
+            pd = keep ? pij * rp : 0.f;
+          }
           ds = pij * (dp - dsum[row]);
+          pij = pd;
         }
       }
       const int ni = min(32, rhi - i0);

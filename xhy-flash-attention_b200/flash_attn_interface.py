@@ -15,7 +15,12 @@ Behaviour kept from the reference:
   * causal masks are TOP-LEFT aligned                                            (tests/test_flash_attn.py:144-146)
   * packed inputs get one packed gradient tensor                                (:108-113,167-176)
 
-Dropout (``dropout_p > 0``) is not implemented in this build and raises.
+Dropout (``dropout_p > 0``) and ``return_attn_probs`` (``S_dmask``) are served by the generic SIMT kernels with a
+Philox-4x32-10 mask and the reference's 8-bit keep threshold (csrc/flash_attn/src/softmax.h:381-447); the random stream
+is this library's own (one Philox call per 16 columns of a row), so masks are reproducible from ``rng_state`` but not
+bit-identical to the reference's -- the reference's tests check dropout through ``S_dmask`` and the drop fraction,
+which is how tests/test_dropout_gpu.py checks it here.  ``S_dmask`` is plain row-major
+(batch, heads, seqlen_q_rounded, seqlen_k_rounded): softmax probabilities, negated where dropped.
 
 Added on top of the reference surface (keyword-only, all default to the reference behaviour):
 ``window_size``, ``flashmask`` (the fork's column-sparse mask vectors), ``flash_attn_with_kvcache``
@@ -84,6 +89,13 @@ def _fill_mask(p: Params, mask: _Mask, b: int, sk: int, keep: list):
         p.flashmask_maxmin = ws.data_ptr()
 
 
+def _new_rng_state():
+    """(seed, offset) for the Philox dropout mask, drawn from torch's CPU generator (reproducible under
+    ``torch.manual_seed``); kept as a small CPU tensor so that saving it for backward costs no device sync.  The
+    reference saves the CUDA generator's philox state the same way (csrc/flash_attn/flash_api.cpp:300-316)."""
+    return torch.randint(0, 2 ** 62, (2,), dtype=torch.int64)
+
+
 def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softmax, mask: _Mask = _NO_MASK,
                         cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=None, max_seqlen_k=None,
                         seqused_k=None):
@@ -91,8 +103,8 @@ def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softma
 
     Returns ``(out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state)`` like the reference binding.
     """
-    if dropout_p > 0.0:
-        raise NotImplementedError("dropout is not implemented in the B200 build (SURVEY.md 8(f))")
+    if not 0.0 <= dropout_p < 1.0:
+        raise ValueError("dropout_p must be in [0, 1)")
     q, k, v = [_maybe_contiguous(x) for x in (q, k, v)]
     if not q.is_cuda:
         raise RuntimeError("q must be on CUDA device")  # flash_api.cpp:209
@@ -128,10 +140,18 @@ def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softma
     p.softmax_scale = softmax_scale
     p.is_causal = 1 if causal else 0
     _fill_mask(p, mask, b, sk, keep)
+    rng_state = S_dmask = None
+    if dropout_p > 0.0:
+        rng_state = _new_rng_state()
+        p.p_dropout = dropout_p
+        p.philox_seed, p.philox_offset = int(rng_state[0]), int(rng_state[1])
+        if return_softmax:   # (b, h, sq_rounded, sk_rounded), probabilities negated where dropped (flash_api.cpp:276-279)
+            S_dmask = torch.empty((b, h, p.seqlen_q_rounded, p.seqlen_k_rounded), dtype=q.dtype, device=q.device)
+            p.s_dmask = S_dmask.data_ptr()
     with torch.cuda.device(q.device):
         _capi.check(_capi.load().fa_b200_fwd(p, _capi.stream_ptr(q.device)), "fa_b200_fwd")
     out = out_p[..., :d_og] if d != d_og else out_p
-    return out, q_p, k_p, v_p, out_p, lse, None, None
+    return out, q_p, k_p, v_p, out_p, lse, S_dmask, rng_state
 
 
 def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p, softmax_scale, causal,
@@ -178,6 +198,11 @@ def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p,
     p.is_causal = 1 if causal else 0
     p.deterministic = 1 if deterministic else 0
     _fill_mask(p, mask, b, sk, keep)
+    if dropout_p > 0.0:
+        if rng_state is None:
+            raise RuntimeError("backward with dropout needs the rng_state saved by forward")
+        p.p_dropout = dropout_p
+        p.philox_seed, p.philox_offset = int(rng_state[0]), int(rng_state[1])
     with torch.cuda.device(q.device):
         _capi.check(_capi.load().fa_b200_bwd(p, _capi.stream_ptr(q.device)), "fa_b200_bwd")
     return dq, dk, dv, softmax_d
@@ -207,6 +232,7 @@ class FlashAttnQKVPackedFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
             qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], dropout_p, softmax_scale, causal=causal,
             return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
         ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
         return out if not return_softmax else (out, softmax_lse, S_dmask)
@@ -217,7 +243,7 @@ class FlashAttnQKVPackedFunc(torch.autograd.Function):
         qkv_shape = q.shape[:-2] + (3, *q.shape[-2:])
         dqkv = torch.empty(qkv_shape, dtype=q.dtype, device=q.device)
         _flash_attn_backward(dout, q, k, v, out, softmax_lse, dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2],
-                             ctx.dropout_p, ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+                             ctx.dropout_p, ctx.softmax_scale, ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dqkv = dqkv[..., :dout.shape[-1]]  # the head dimension may have been padded
         return dqkv, None, None, None, None, None
 
@@ -230,6 +256,7 @@ class FlashAttnVarlenQKVPackedFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
             qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens, max_seqlen, max_seqlen, dropout_p,
             softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens)
         ctx.dropout_p, ctx.max_seqlen, ctx.softmax_scale, ctx.causal, ctx.mask = \
             dropout_p, max_seqlen, softmax_scale, causal, mask
@@ -242,7 +269,7 @@ class FlashAttnVarlenQKVPackedFunc(torch.autograd.Function):
         dqkv = torch.empty(qkv_shape, dtype=q.dtype, device=q.device)
         _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dqkv[:, 0], dqkv[:, 1], dqkv[:, 2],
                                     cu_seqlens, cu_seqlens, ctx.max_seqlen, ctx.max_seqlen, ctx.dropout_p,
-                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dqkv = dqkv[..., :dout.shape[-1]]
         return dqkv, None, None, None, None, None, None, None
 
@@ -255,6 +282,7 @@ class FlashAttnKVPackedFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
             q, kv[:, :, 0], kv[:, :, 1], dropout_p, softmax_scale, causal=causal,
             return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
         ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
         return out if not return_softmax else (out, softmax_lse, S_dmask)
@@ -266,7 +294,7 @@ class FlashAttnKVPackedFunc(torch.autograd.Function):
         kv_shape = k.shape[:-2] + (2, *k.shape[-2:])
         dkv = torch.empty(kv_shape, dtype=k.dtype, device=k.device)
         _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dkv[:, :, 0], dkv[:, :, 1], ctx.dropout_p,
-                             ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+                             ctx.softmax_scale, ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dq = dq[..., :dout.shape[-1]]
         dkv = dkv[..., :dout.shape[-1]]
         return dq, dkv, None, None, None, None, None
@@ -281,6 +309,7 @@ class FlashAttnVarlenKVPackedFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
             q, kv[:, 0], kv[:, 1], cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
             softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens_q, cu_seqlens_k)
         ctx.dropout_p, ctx.max_seqlen_q, ctx.max_seqlen_k = dropout_p, max_seqlen_q, max_seqlen_k
         ctx.softmax_scale, ctx.causal, ctx.mask = softmax_scale, causal, mask
@@ -294,7 +323,7 @@ class FlashAttnVarlenKVPackedFunc(torch.autograd.Function):
         dkv = torch.empty(kv_shape, dtype=k.dtype, device=k.device)
         _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dq, dkv[:, 0], dkv[:, 1], cu_seqlens_q,
                                     cu_seqlens_k, ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p,
-                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask)
+                                    ctx.softmax_scale, ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dq = dq[..., :dout.shape[-1]]
         dkv = dkv[..., :dout.shape[-1]]
         return dq, dkv, None, None, None, None, None, None, None, None, None
@@ -308,6 +337,7 @@ class FlashAttnFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_forward(
             q, k, v, dropout_p, softmax_scale, causal=causal, return_softmax=return_softmax and dropout_p > 0,
             mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse)
         ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.mask = dropout_p, softmax_scale, causal, mask
         return out if not return_softmax else (out, softmax_lse, S_dmask)
@@ -317,7 +347,7 @@ class FlashAttnFunc(torch.autograd.Function):
         q, k, v, out, softmax_lse = ctx.saved_tensors
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
         _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, ctx.dropout_p, ctx.softmax_scale,
-                             ctx.causal, mask=ctx.mask)
+                             ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dq = dq[..., :dout.shape[-1]]
         dk = dk[..., :dout.shape[-1]]
         dv = dv[..., :dout.shape[-1]]
@@ -333,6 +363,7 @@ class FlashAttnVarlenFunc(torch.autograd.Function):
         out, q, k, v, out_padded, softmax_lse, S_dmask, rng_state = _flash_attn_varlen_forward(
             q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
             causal=causal, return_softmax=return_softmax and dropout_p > 0, mask=mask)
+        ctx.rng_state = rng_state
         ctx.save_for_backward(q, k, v, out_padded, softmax_lse, cu_seqlens_q, cu_seqlens_k)
         ctx.dropout_p, ctx.max_seqlen_q, ctx.max_seqlen_k = dropout_p, max_seqlen_q, max_seqlen_k
         ctx.softmax_scale, ctx.causal, ctx.mask = softmax_scale, causal, mask
@@ -344,7 +375,7 @@ class FlashAttnVarlenFunc(torch.autograd.Function):
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
         _flash_attn_varlen_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
                                     ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p, ctx.softmax_scale,
-                                    ctx.causal, mask=ctx.mask)
+                                    ctx.causal, mask=ctx.mask, rng_state=ctx.rng_state)
         dq = dq[..., :dout.shape[-1]]
         dk = dk[..., :dout.shape[-1]]
         dv = dv[..., :dout.shape[-1]]
