@@ -85,6 +85,12 @@ typedef struct fa_b200_params {
   uint64_t philox_seed, philox_offset; /* keep iff philox_byte(seed, offset, b, h, row, col) <= floor(255 * (1 - p)) */
   void    *s_dmask;               /* optional (b, h, seqlen_q_rounded, seqlen_k_rounded) in the element type: softmax
                                      probabilities, NEGATED where the weight was dropped (return_softmax), or NULL */
+
+  /* ---- dense additive mask (reference: csrc/flash_attn/src/softmax.h:360-379, flash_fwd_kernel.h:1104-1107) ---- */
+  const void *attn_mask;          /* (b, mask_head_mod, mask_seq_mod, seqlen_k) in the element type, or NULL:
+                                     logits = scale * (q.k + mask[b, h % head_mod, row % seq_mod, col] * unscale_softmax) */
+  int32_t mask_head_mod, mask_seq_mod;
+  float   unscale_softmax;
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

@@ -140,7 +140,8 @@ def attention_ref(q, k, v, query_padding_mask=None, key_padding_mask=None, dropo
 
 def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_scale: Optional[float] = None,
                          upcast: bool = True, reorder_ops: bool = False,
-                         lse_empty: float = float("inf")) -> Tuple[torch.Tensor, torch.Tensor]:
+                         lse_empty: float = float("inf"), bias: Optional[torch.Tensor] = None
+                         ) -> Tuple[torch.Tensor, torch.Tensor]:
     """General oracle: arbitrary boolean mask (broadcastable to (b, h, sq, sk); True = masked).
 
     Returns (out (b,sq,h,d) in q.dtype, lse (b,h,sq) fp32).  Rows with every key
@@ -164,6 +165,8 @@ def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_s
         scores = torch.einsum("bthd,bshd->bhts", q * scale, k)
     else:
         scores = torch.einsum("bthd,bshd->bhts", q, k * scale)
+    if bias is not None:   # dense additive mask, broadcastable to (b, h, sq, sk) (csrc/flash_attn/src/softmax.h:360-379)
+        scores = scores + bias.to(scores.dtype)
     if mask is not None:
         scores = scores.masked_fill(mask.to(scores.device), NEG_INF)
     lse = torch.logsumexp(scores.float(), dim=-1)
@@ -175,7 +178,7 @@ def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_s
     return out.to(dtype_og), lse
 
 
-def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=True, reorder_ops=False):
+def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=True, reorder_ops=False, bias=None):
     """(out, lse, dq, dk, dv) by autograd through ``attention_masked_ref``.
 
     This is how the reference's tests obtain gradients of the oracle
@@ -184,7 +187,7 @@ def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=Tru
     q_ = q.detach().clone().requires_grad_(True)
     k_ = k.detach().clone().requires_grad_(True)
     v_ = v.detach().clone().requires_grad_(True)
-    out, lse = attention_masked_ref(q_, k_, v_, mask, softmax_scale, upcast, reorder_ops)
+    out, lse = attention_masked_ref(q_, k_, v_, mask, softmax_scale, upcast, reorder_ops, bias=bias)
     dq, dk, dv = torch.autograd.grad(out, (q_, k_, v_), dout.to(out.dtype))
     return out.detach(), lse.detach(), dq, dk, dv
 

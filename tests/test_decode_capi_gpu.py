@@ -247,3 +247,55 @@ def test_decode_window(fa, window, sq):
     (ref, pt), lse_ref = _kvcache_ref(q, kc, vc, seqlens, False, window)
     check_2x("out", out, ref, pt)
     check_lse(lse, lse_ref)
+
+
+@pytest.mark.parametrize("mh,ms", [(1, 1), (4, 1), (1, 200), (4, 200)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_flat_capi_dense_attn_mask(capi, mh, ms, causal):
+    """flash_attn_fwd / flash_attn_bwd with the dense additive attn_mask of the flat ABI (csrc/capi/flash_attn.h:36-37):
+    logits = scale * q.k + mask, mask (b, 1-or-h, 1-or-sq, sk) broadcast by h % mod / row % mod."""
+    lib = capi.load()
+    torch.manual_seed(0)
+    b, sq, sk, h, d = 2, 200, 264, 4, 64
+    q, g = [torch.randn(b, sq, h, d, device=DEV, dtype=torch.float16) for _ in range(2)]
+    k, v = [torch.randn(b, sk, h, d, device=DEV, dtype=torch.float16) for _ in range(2)]
+    bias = (torch.randn(b, mh, ms, sk, device=DEV) * 2).to(torch.float16)
+    bias[:, :, :, 250:] = float("-inf")                       # a padded key tail expressed through the mask
+    out, dq, dk, dv = torch.empty_like(q), torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    sq_r, sk_r = capi.round_up(sq, 128), capi.round_up(sk, 128)
+    lse = torch.empty(b, h, sq, device=DEV, dtype=torch.float32)
+    softmax_d = torch.empty(b, h, sq_r, device=DEV, dtype=torch.float32)
+    dq_accum = torch.empty(b, h, sq_r, d, device=DEV, dtype=torch.float32)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    vp = lambda t: C.c_void_p(t.data_ptr() if t is not None else None)
+    i32 = C.c_int
+    st = lambda t: (i32(t.stride(1)), i32(t.stride(2)), i32(t.stride(0)))  # row, head, batch
+    (qr, qh, qb), (kr, kh, kb), (vr, vh, vb), (or_, oh, ob) = st(q), st(k), st(v), st(out)
+    dims = (C.c_int64 * 4)(b, mh, ms, sk)
+    scale = d ** -0.5
+    lib.flash_attn_fwd.restype = C.c_bool
+    ok = lib.flash_attn_fwd(
+        vp(q), vp(k), vp(v), None, vp(out), None, vp(lse), i32(b), i32(sq), i32(sk), i32(sq_r), i32(sk_r), i32(h),
+        i32(h), i32(d), i32(d), C.c_float(0.0), C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal), C.c_bool(False),
+        C.c_bool(False), stream, C.c_uint64(0), C.c_uint64(0), vp(bias), dims, None, None, None, None, None, None,
+        qr, kr, vr, qh, kh, vh, or_, oh, qb, kb, vb, ob)
+    assert ok, capi.last_error()
+    (dqr, dqh, dqb), (dkr, dkh, dkb), (dvr, dvh, dvb), (gr, gh, gb) = st(dq), st(dk), st(dv), st(g)
+    lib.flash_attn_bwd.restype = C.c_bool
+    ok = lib.flash_attn_bwd(
+        vp(g), vp(q), vp(k), vp(v), vp(out), vp(softmax_d), vp(lse), None, vp(dq), vp(dk), vp(dv), vp(dq_accum),
+        i32(b), i32(sq), i32(sk), i32(sq_r), i32(sk_r), i32(h), i32(h), i32(d), i32(d), C.c_float(0.0),
+        C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal), C.c_bool(False), i32(0), stream, C.c_uint64(0),
+        C.c_uint64(0), vp(bias), dims, None, None, None, None, None, None,
+        qr, kr, vr, qh, kh, vh, or_, oh, qb, kb, vb, ob, dqr, dkr, dvr, dqh, dkh, dvh, gr, gh, dqb, dkb, dvb, gb)
+    assert ok, capi.last_error()
+    torch.cuda.synchronize()
+    mask = orc.causal_mask_top_left(sq, sk).to(DEV) if causal else None
+    bias_full = bias.float().expand(b, mh, sq if ms == 1 else ms, sk)
+    ref = orc.attention_grads_ref(q, k, v, g, mask, bias=bias_full)
+    pt = orc.attention_grads_ref(q, k, v, g, mask, upcast=False, reorder_ops=True, bias=bias_full)
+    check_2x("out", out, ref[0], pt[0])
+    check_lse(lse, ref[1])
+    check_2x("dq", dq, ref[2], pt[2])
+    check_2x("dk", dk, ref[3], pt[3])
+    check_2x("dv", dv, ref[4], pt[4])

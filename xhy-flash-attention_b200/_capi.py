@@ -46,6 +46,8 @@ class Params(C.Structure):
         ("dkv_expanded", C.c_int32), ("deterministic", C.c_int32), ("force_generic", C.c_int32),
         ("num_splits", C.c_int32), ("oaccum", C.c_void_p), ("lseaccum", C.c_void_p),
         ("p_dropout", C.c_float), ("philox_seed", C.c_uint64), ("philox_offset", C.c_uint64), ("s_dmask", C.c_void_p),
+        ("attn_mask", C.c_void_p), ("mask_head_mod", C.c_int32), ("mask_seq_mod", C.c_int32),
+        ("unscale_softmax", C.c_float),
     ]
 
 

@@ -61,6 +61,7 @@ static void check_common(const Params &p) {
   FA_CHECK(p.d > 0 && p.d % 8 == 0 && p.d <= 256, "head_size must be a multiple of 8 and <= 256");
   FA_CHECK(p.q.ptr && p.k.ptr && p.v.ptr, "q, k, v must be set");
   FA_CHECK(device_cc_major() >= 10, "libflashattn_b200 needs a Blackwell (sm_100a) device");
+  if (p.attn_mask) FA_CHECK(p.mask_head_mod > 0 && p.mask_seq_mod > 0, "attn_mask needs mask_head_mod and mask_seq_mod");
   if (p.lt_start) {
     FA_CHECK(p.h_mask > 0 && p.h % p.h_mask == 0, "flashmask heads must divide num_heads");
   } else {
@@ -74,7 +75,7 @@ void run_fwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   // dropout / return_softmax take the generic kernels (Philox per element); the tcgen05 kernels are dropout-free
-  const bool special = p.p_dropout > 0.f || p.s_dmask != nullptr;
+  const bool special = p.p_dropout > 0.f || p.s_dmask != nullptr || p.attn_mask != nullptr;
   if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
   else generic_fwd(p, s);
 }
@@ -85,7 +86,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.softmax_d, "softmax_d workspace must be set");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
-  if (!p.force_generic && !(p.p_dropout > 0.f) && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
+  if (!p.force_generic && !(p.p_dropout > 0.f) && p.attn_mask == nullptr && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }
 

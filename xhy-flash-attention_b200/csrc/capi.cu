@@ -43,6 +43,18 @@ fa_b200_tensor tensor(const void *ptr, int batch_stride, int row_stride, int hea
   return t;
 }
 
+// dense additive mask: mask_dims = (batch, 1-or-heads, 1-or-seqlen_q, seqlen_k)  (csrc/capi/flash_attn.cu:78-83)
+void set_attn_mask(Params &p, const void *attn_mask, const int64_t *mask_dims, float softmax_unscale) {
+  if (!attn_mask) return;
+  FA_CHECK(mask_dims != nullptr, "mask_dims must be given with attn_mask");
+  FA_CHECK(mask_dims[0] == p.b && mask_dims[3] == p.seqlen_k, "mask_dims must be (batch, 1 or heads, 1 or seqlen_q, seqlen_k)");
+  FA_CHECK(mask_dims[1] == 1 || mask_dims[1] == p.h, "mask_dims[1] must be 1 or num_heads");
+  FA_CHECK(mask_dims[2] == 1 || mask_dims[2] == p.seqlen_q, "mask_dims[2] must be 1 or seqlen_q");
+  p.attn_mask = attn_mask;
+  p.mask_head_mod = (int)mask_dims[1]; p.mask_seq_mod = (int)mask_dims[2];
+  p.unscale_softmax = softmax_unscale;
+}
+
 void set_flashmask(Params &p, const void *downstart, const int64_t *dims, const void *upend, const void *downend,
                    const void *upstart, const void *maxmin) {
   if (!downstart && !upend && !downend && !upstart) return;
@@ -89,9 +101,9 @@ bool flash_attn_fwd(
     int v_row_stride, int q_head_stride, int k_head_stride, int v_head_stride, int o_row_stride, int o_head_stride,
     int q_batch_stride, int k_batch_stride, int v_batch_stride, int o_batch_stride) {
   FA_BEGIN
-  unsupported(attn_mask != nullptr, "dense attn_mask");
   Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
                          head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  set_attn_mask(p, attn_mask, mask_dims, softmax_unscale);
   p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;   // csrc/capi/flash_attn.cu:672-677
   if (return_softmax) {
     FA_CHECK(softmax_ptr != nullptr, "return_softmax needs softmax_ptr");
@@ -108,7 +120,7 @@ bool flash_attn_fwd(
     uint64_t st[2] = {seed, offset};
     FA_CUDA(cudaMemcpyAsync(rng_state, st, sizeof(st), cudaMemcpyHostToDevice, stream));
   }
-  (void)softmax_ptr; (void)softmax_unscale; (void)mask_dims;
+  (void)softmax_ptr;
   fa::run_fwd(p, stream);
   FA_END
 }
@@ -162,9 +174,9 @@ bool flash_attn_bwd(
     int dq_head_stride, int dk_head_stride, int dv_head_stride, int do_row_stride, int do_head_stride,
     int dq_batch_stride, int dk_batch_stride, int dv_batch_stride, int do_batch_stride) {
   FA_BEGIN
-  unsupported(attn_mask != nullptr, "dense attn_mask");
   Params p = base_params(batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads, num_heads_k,
                          head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  set_attn_mask(p, attn_mask, mask_dims, softmax_unscale);
   p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
@@ -181,7 +193,7 @@ bool flash_attn_bwd(
   p.deterministic = (num_splits == 1);      // csrc/flash_attn/src/flash_bwd_kernel.h:3203-3208
   set_flashmask(p, flashmask_downstart_ptr, flashmask_dims, flashmask_upend_ptr, flashmask_downend_ptr,
                 flashmask_upstart_ptr, flashmask_maxmin_ptr);
-  (void)rng_state; (void)seed; (void)offset; (void)softmax_unscale; (void)mask_dims;
+  (void)rng_state;
   fa::run_bwd(p, stream);
   FA_END
 }

@@ -60,6 +60,16 @@ __device__ __forceinline__ float dot_row(const float *__restrict__ a, const T *_
   return acc;
 }
 
+// dense additive mask term, already multiplied by unscale_softmax (0 when there is no mask):
+// csrc/flash_attn/src/softmax.h:360-379 adds it to the unscaled score, row offset as flash_fwd_kernel.h:1104-1107
+template <typename T>
+__device__ __forceinline__ float mask_term(const Params &p, int bi, int hq, int row, int col) {
+  if (p.attn_mask == nullptr) return 0.f;
+  const int64_t off = ((((int64_t)bi * p.mask_head_mod + hq % p.mask_head_mod) * p.mask_seq_mod + row % p.mask_seq_mod) *
+                       (int64_t)p.seqlen_k) + col;
+  return to_f(((const T *)p.attn_mask)[off]) * p.unscale_softmax;
+}
+
 struct Seq {
   int q_row0, k_row0, sq, sk;
   int64_t q_boff, k_boff;  // batch offsets in units of batch_stride multipliers (0 or bi)
@@ -131,7 +141,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
   for (int j0 = lo; j0 < hi; j0 += 32) {
     const int col = j0 + lane;
     float s = -CUDART_INF_F;
-    if (col < hi && !is_masked(m, row, col)) s = dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) * scale_log2;
+    if (col < hi && !is_masked(m, row, col))
+      s = (dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) * scale_log2;
     const float mnew = fmaxf(mx, warp_max(s));
     if (mnew == -CUDART_INF_F) continue;  // nothing visible so far (warp-uniform)
     const float corr = exp2f(mx - mnew);  // mx = -inf -> 0
@@ -165,7 +176,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
       const int col = j0 + lane;
       float pr = 0.f;
       if (!empty && col >= lo && col < hi && !is_masked(m, row, col)) {
-        pr = exp2f(dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) * scale_log2 - lse2);
+        pr = exp2f((dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
+                       scale_log2 - lse2);
         if (drop && !dropout_keep(dc, col)) pr = -pr;
       }
       if (col < p.seqlen_k_rounded) sd[col] = from_f<T>(pr);
@@ -251,7 +263,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
     const int col = j0 + lane;
     float ds = 0.f;
     if (col < hi && !is_masked(m, row, col)) {
-      const float sc = dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) * scale_log2;
+      const float sc = (dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
+                       scale_log2;
       const float pij = exp2f(sc - lse2);
       float dp = dot_row(g_s[warp], vbase + (int64_t)col * p.v.row_stride, d);
       if (drop) dp = dropout_keep(dc, col) ? dp * rp : 0.f;   // dP = keep / p_keep * (dO . V)
@@ -318,7 +331,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
       if (row < rhi && !is_masked(m, row, col)) {
         const float l = lse[row];
         if (!isinf(l)) {
-          const float sc = dot_row(k_s[warp], qbase + (int64_t)row * p.q.row_stride, d) * scale_log2;
+          const float sc = (dot_row(k_s[warp], qbase + (int64_t)row * p.q.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
+                           scale_log2;
           pij = exp2f(sc - l * kLog2e);
           float dp = dot_row(v_s[warp], gbase + (int64_t)row * p.dout.row_stride, d);
           float pd = pij;                                  // the weight dV sees: keep / p_keep * P
