@@ -41,7 +41,7 @@ template <int HD> struct FwdSmem {
   static constexpr int kQOff = 0;
   static constexpr int kKVOff = kTilesPerCta * kTileBytes;
   static constexpr int kBarOff = kKVOff + kStages * kTileBytes;
-  static constexpr int kNumBars = 2 + 2 + kStages * 2 + 2 + 2 + 2;
+  static constexpr int kNumBars = 2 + 2 + kStages * 2 + 2 + 2 + 2 + 2;
   static constexpr int kTmemSlotOff = kBarOff + kNumBars * 8;
   // FlashMask: record ring + its barriers, and per softmax warpgroup the staged mask vectors of one key block
   static constexpr int kFmRecOff = (kTmemSlotOff + 16 + 31) / 32 * 32;
@@ -309,7 +309,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
   // barrier addresses
   auto bar = [&](int i) { return sbase + L::kBarOff + i * 8; };
   const int B_QFULL = 0, B_QEMPTY = 2, B_KVFULL = 4, B_KVEMPTY = 4 + kStages, B_SFULL = 4 + 2 * kStages,
-            B_PFULL = B_SFULL + 2, B_OFULL = B_PFULL + 2;
+            B_PFULL = B_SFULL + 2, B_OFULL = B_PFULL + 2, B_PHALF = B_OFULL + 2;
   uint32_t *tmem_slot = (uint32_t *)(smem + L::kTmemSlotOff);
   const FmRing fm_ring = {sbase + L::kFmRecOff, sbase + L::kFmBarOff, sbase + L::kFmBarOff + kFmRing * 8};
 
@@ -319,6 +319,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       mbar_init(bar(B_QEMPTY + t), kBM);
       mbar_init(bar(B_SFULL + t), 1);
       mbar_init(bar(B_PFULL + t), kBM);
+      mbar_init(bar(B_PHALF + t), kBM);
       mbar_init(bar(B_OFULL + t), 1);
     }
     for (int s = 0; s < kStages; ++s) {
@@ -422,14 +423,19 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         }
         __syncwarp();
       };
-      auto issue_pv = [&](int t, uint32_t vstage, bool accumulate) {
+      // O_t += P_t V in two halves of 64 keys: the first half is issued as soon as the softmax warpgroup has stored the
+      // first 64 columns of P (B_PHALF), so it runs under the second half of the exponentials; only the second half is
+      // left on the S -> softmax -> PV -> S dependency chain of the tile.
+      auto issue_pv_half = [&](int t, uint32_t vstage, int half, bool accumulate) {
         const uint32_t va = sbase + L::kKVOff + vstage * L::kTileBytes;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBN / 16; ++k)
+          for (int kk = 0; kk < kBN / 32; ++kk) {
+            const int k = half * (kBN / 32) + kk;
             umma_ts(tmem + 2 * kBN + t * HD, tmem + t * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kHalfBytes, 1024),
                     idesc_o, (accumulate || k > 0) ? 1u : 0u);
-          umma_commit(bar(B_OFULL + t));
+          }
+          if (half == 1) umma_commit(bar(B_OFULL + t));
         }
         __syncwarp();
       };
@@ -469,10 +475,13 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
             if (cur.a[t]) {
+              mbar_wait(bar(B_PHALF + t), pcnt[t] & 1);
+              tc_fence_after();
+              issue_pv_half(t, vst, 0, !first[t]);
               mbar_wait(bar(B_PFULL + t), pcnt[t] & 1);
               ++pcnt[t];
               tc_fence_after();
-              issue_pv(t, vst, !first[t]);
+              issue_pv_half(t, vst, 1, !first[t]);
               first[t] = false;
             }
             if (has_next && nxt.a[t]) {
@@ -677,6 +686,11 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
             pk[i] = pack2<kBf16>(p0, p1);
           }
           tmem_st16(tS + c * 16, pk);
+          if (c == 1) {   // the first 64 columns of P are in TMEM: let the issuer start the first half of PV
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar(B_PHALF + t));
+          }
         }
         {
           float a0, a1;
