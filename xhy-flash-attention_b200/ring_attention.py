@@ -197,11 +197,14 @@ def ring_forward(q, k, v, softmax_scale, causal, group=None, ops: RingOps = _CUD
                 ops.merge(o_acc, lse_acc, o_step.contiguous(), lse_step.contiguous())
             else:  # only the second half of the local queries took part
                 half = s // 2
-                o_half = o_acc[:, half:].contiguous()
-                l_half = lse_acc[:, half:].contiguous()
-                ops.merge(o_half, l_half, o_step.contiguous(), lse_step.contiguous())
-                o_acc[:, half:] = o_half
-                lse_acc[:, half:] = l_half
+                o_view, l_view = o_acc[:, half:], lse_acc[:, half:]
+                if o_view.is_contiguous() and l_view.is_contiguous():      # batch 1: merge in place, no copies
+                    ops.merge(o_view, l_view, o_step.contiguous(), lse_step.contiguous())
+                else:
+                    o_half, l_half = o_view.contiguous(), l_view.contiguous()
+                    ops.merge(o_half, l_half, o_step.contiguous(), lse_step.contiguous())
+                    o_view.copy_(o_half)
+                    l_view.copy_(l_half)
         if rot is not None:
             k_cur, v_cur = rot.wait()
     return o_acc.to(q.dtype), lse_acc.transpose(1, 2).contiguous()
