@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 2
+#define FA_B200_ABI_VERSION 3
 
 /* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
  * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
@@ -91,6 +91,22 @@ typedef struct fa_b200_params {
                                      logits = scale * (q.k + mask[b, h % head_mod, row % seq_mod, col] * unscale_softmax) */
   int32_t mask_head_mod, mask_seq_mod;
   float   unscale_softmax;
+
+  /* ---- KV-cache addressing, softcap, ALiBi (ABI v3; reference: csrc/flash_attn_v3/flash.h:96-140, seqlen.h:56-91,
+   *      paged_kv.h, mainloop_fwd_sm90_tma_gmma_ws.hpp:537-556,639,1064-1067).  Forward only, except softcap/alibi. ---- */
+  const int32_t *page_table;      /* (b, page_table_batch_stride) int32 or NULL.  When set, k/v are
+                                     (num_pages, page_size, h_k, d): batch_stride is the PAGE stride, and key t of batch
+                                     element i is row t % page_size of page page_table[i][t / page_size];
+                                     seqlen_k = pages per sequence * page_size */
+  int64_t page_table_batch_stride;
+  int32_t page_size, num_pages;
+  const int32_t *kv_batch_idx;    /* (b) cache row used by batch element i, or NULL (= i); not with page_table */
+  int32_t b_k;                    /* batch size of the cache when kv_batch_idx is set (0 = b) */
+  const int32_t *leftpad_k;       /* (b) index of the first valid key; seqused_k counts from index 0, so the valid keys
+                                     are [leftpad_k[i], seqused_k[i]) (seqlen.h:73-80) */
+  float   softcap;                /* > 0: logits = softcap * tanh(scale * q.k / softcap)  (before masks and ALiBi) */
+  const float *alibi_slopes;      /* (h) or (b, h) fp32 or NULL: logits -= slope * |col - (row + seqlen_k - seqlen_q)| */
+  int64_t alibi_batch_stride;     /* 0 for (h) */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */
@@ -123,6 +139,23 @@ bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void
                        int64_t new_batch_stride, int64_t new_row_stride, int64_t new_head_stride,
                        int64_t cache_batch_stride, int64_t cache_row_stride, int64_t cache_head_stride,
                        cudaStream_t stream);
+
+/* Same, for every cache layout fa_b200_params can describe: uses p->k / p->v (cache), p->page_table, p->kv_batch_idx
+ * and p->seqused_k (the lengths BEFORE the append; NULL = 0); new rows go to positions seqused_k[i] .. + seqlen_new.
+ * k_new / v_new: (b, seqlen_new, h_k, d). */
+bool fa_b200_append_kv_paged(const fa_b200_params *p, const void *k_new, const void *v_new, int seqlen_new,
+                             int64_t new_batch_stride, int64_t new_row_stride, int64_t new_head_stride,
+                             cudaStream_t stream);
+
+/* Rotary embedding, out-of-place (reference: csrc/flash_attn_v3/rotary.h; flash_attn_with_kvcache's rotary_cos /
+ * rotary_sin): x, out (b, s, h, d); cos, sin (seqlen_ro, rotary_dim / 2) in the element type.  Row r of batch element
+ * i is rotated at position seqlen_offsets[i] + (fixed_position ? 0 : r) (seqlen_offsets NULL = 0).  interleaved pairs
+ * (2j, 2j+1), otherwise (j, j + rotary_dim/2); columns >= rotary_dim are copied.  fp32 arithmetic, one rounding. */
+bool fa_b200_rotary(const void *x, void *out, const void *cos, const void *sin, const int32_t *seqlen_offsets,
+                    int batch, int seqlen, int num_heads, int head_size, int rotary_dim, int seqlen_ro,
+                    int interleaved, int fixed_position, int is_bf16,
+                    int64_t x_batch_stride, int64_t x_row_stride, int64_t x_head_stride,
+                    int64_t out_batch_stride, int64_t out_row_stride, int64_t out_head_stride, cudaStream_t stream);
 
 /* FlashMask block min/max scan (reference: csrc/flashmask_v2/flash_mask.hpp:162-245; order
  * [lts_max, lts_min, ute_max, ute_min, lte_max, lte_min, uts_max, uts_min]). Exposed for tests. */

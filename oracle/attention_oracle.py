@@ -140,8 +140,8 @@ def attention_ref(q, k, v, query_padding_mask=None, key_padding_mask=None, dropo
 
 def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_scale: Optional[float] = None,
                          upcast: bool = True, reorder_ops: bool = False,
-                         lse_empty: float = float("inf"), bias: Optional[torch.Tensor] = None
-                         ) -> Tuple[torch.Tensor, torch.Tensor]:
+                         lse_empty: float = float("inf"), bias: Optional[torch.Tensor] = None,
+                         softcap: float = 0.0) -> Tuple[torch.Tensor, torch.Tensor]:
     """General oracle: arbitrary boolean mask (broadcastable to (b, h, sq, sk); True = masked).
 
     Returns (out (b,sq,h,d) in q.dtype, lse (b,h,sq) fp32).  Rows with every key
@@ -165,6 +165,8 @@ def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_s
         scores = torch.einsum("bthd,bshd->bhts", q * scale, k)
     else:
         scores = torch.einsum("bthd,bshd->bhts", q, k * scale)
+    if softcap > 0.0:      # tanh soft-capping of the scaled scores, before bias and masks
+        scores = softcap * torch.tanh(scores / softcap)   # (csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:537-556)
     if bias is not None:   # dense additive mask, broadcastable to (b, h, sq, sk) (csrc/flash_attn/src/softmax.h:360-379)
         scores = scores + bias.to(scores.dtype)
     if mask is not None:
@@ -178,7 +180,8 @@ def attention_masked_ref(q, k, v, mask: Optional[torch.Tensor] = None, softmax_s
     return out.to(dtype_og), lse
 
 
-def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=True, reorder_ops=False, bias=None):
+def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=True, reorder_ops=False, bias=None,
+                        softcap=0.0):
     """(out, lse, dq, dk, dv) by autograd through ``attention_masked_ref``.
 
     This is how the reference's tests obtain gradients of the oracle
@@ -187,7 +190,7 @@ def attention_grads_ref(q, k, v, dout, mask=None, softmax_scale=None, upcast=Tru
     q_ = q.detach().clone().requires_grad_(True)
     k_ = k.detach().clone().requires_grad_(True)
     v_ = v.detach().clone().requires_grad_(True)
-    out, lse = attention_masked_ref(q_, k_, v_, mask, softmax_scale, upcast, reorder_ops, bias=bias)
+    out, lse = attention_masked_ref(q_, k_, v_, mask, softmax_scale, upcast, reorder_ops, bias=bias, softcap=softcap)
     dq, dk, dv = torch.autograd.grad(out, (q_, k_, v_), dout.to(out.dtype))
     return out.detach(), lse.detach(), dq, dk, dv
 
@@ -273,3 +276,97 @@ def attention_flops(batch, seqlen_q, seqlen_k, nheads, headdim, causal, mode="fw
     assert mode in ("fwd", "bwd", "fwd_bwd")
     f = 4 * batch * seqlen_q * seqlen_k * nheads * headdim // (2 if causal else 1)
     return f if mode == "fwd" else (2.5 * f if mode == "bwd" else 3.5 * f)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# KV-cache decode extras (csrc/flash_attn_v3: rotary.h, paged_kv.h, seqlen.h:56-91, mainloop softcap :537-556)
+# ---------------------------------------------------------------------------------------------------------------------
+def rotary_ref(x, cos, sin, positions, interleaved=True):
+    """Rotary embedding of x (b, s, h, d) at integer ``positions`` (b, s): pairs (2j, 2j+1) when ``interleaved`` else
+    (j, j + rotary_dim/2); x1' = x1 cos - x2 sin, x2' = x1 sin + x2 cos, computed in fp32 and rounded once
+    (csrc/flash_attn_v3/rotary.h apply_rotary_interleaved / apply_rotary_contiguous).  cos, sin: (seqlen_ro, rotary_dim/2)."""
+    b, s, h, d = x.shape
+    half = cos.shape[-1]
+    rdim = 2 * half
+    c = cos.float()[positions.long()].unsqueeze(2)          # (b, s, 1, half)
+    sn = sin.float()[positions.long()].unsqueeze(2)
+    xr = x[..., :rdim].float()
+    if interleaved:
+        x1, x2 = xr[..., 0::2], xr[..., 1::2]
+        o = torch.stack((x1 * c - x2 * sn, x1 * sn + x2 * c), dim=-1).reshape(b, s, h, rdim)
+    else:
+        x1, x2 = xr[..., :half], xr[..., half:]
+        o = torch.cat((x1 * c - x2 * sn, x1 * sn + x2 * c), dim=-1)
+    return torch.cat((o.to(x.dtype), x[..., rdim:]), dim=-1)
+
+
+def alibi_bias(slopes, sq, sk):
+    """ALiBi bias -slope * |i + sk - sq - j| for slopes (h,) or (b, h) -> (1 or b, h, sq, sk) fp32."""
+    i = torch.arange(sq, device=slopes.device).view(-1, 1)
+    j = torch.arange(sk, device=slopes.device).view(1, -1)
+    dist = (i + sk - sq - j).abs().float()
+    sl = slopes.float()
+    sl = sl.view(1, -1, 1, 1) if sl.dim() == 1 else sl.view(sl.shape[0], sl.shape[1], 1, 1)
+    return -sl * dist
+
+
+def kvcache_ref(q, k_cache, v_cache, k=None, v=None, rotary_cos=None, rotary_sin=None, cache_seqlens=None,
+                cache_batch_idx=None, cache_leftpad=None, block_table=None, softmax_scale=None, causal=False,
+                window_size=(-1, -1), softcap=0.0, rotary_interleaved=True, alibi_slopes=None, upcast=True):
+    """flash_attn_with_kvcache restated with plain indexing, one batch element at a time.
+
+    Returns (out (b, sq, h, d), lse (b, h, sq), k_cache', v_cache') -- the caches are updated COPIES.
+    Valid keys of element i are the physical rows [leftpad_i, cache_seqlens_i (+ seqlen_new)) of cache row
+    cache_batch_idx[i], or of the pages block_table[i] laid end to end."""
+    b, sq, h, d = q.shape
+    k_cache, v_cache = k_cache.clone(), v_cache.clone()
+    if cache_seqlens is None:
+        lens = torch.zeros(b, dtype=torch.long)
+    elif isinstance(cache_seqlens, int):
+        lens = torch.full((b,), cache_seqlens, dtype=torch.long)
+    else:
+        lens = cache_seqlens.long().cpu()
+    lp = torch.zeros(b, dtype=torch.long) if cache_leftpad is None else cache_leftpad.long().cpu()
+    local = tuple(window_size) != (-1, -1)
+    s_new = 0 if k is None else k.shape[1]
+    if rotary_cos is not None:
+        pos_k = lens.view(b, 1).to(q.device) + torch.arange(s_new, device=q.device).view(1, -1)
+        k = rotary_ref(k, rotary_cos, rotary_sin, pos_k, rotary_interleaved)
+        if causal or local:
+            pos_q = lens.view(b, 1).to(q.device) + torch.arange(sq, device=q.device).view(1, -1)
+        else:
+            pos_q = lens.view(b, 1).to(q.device).expand(b, sq)
+        q = rotary_ref(q, rotary_cos, rotary_sin, pos_q, rotary_interleaved)
+    outs, lses = [], []
+    for i in range(b):
+        if block_table is not None:
+            page_size = k_cache.shape[1]
+            rows = lambda lo, hi: (block_table[i].long()[torch.arange(lo, hi) // page_size], torch.arange(lo, hi) % page_size)
+        else:
+            slab = i if cache_batch_idx is None else int(cache_batch_idx[i])
+            rows = lambda lo, hi: (torch.full((hi - lo,), slab, dtype=torch.long), torch.arange(lo, hi))
+        n0 = int(lens[i])
+        if k is not None:
+            a, r = rows(n0, n0 + s_new)
+            k_cache[a.to(q.device), r.to(q.device)] = k[i]
+            v_cache[a.to(q.device), r.to(q.device)] = v[i]
+        a, r = rows(int(lp[i]), n0 + s_new)
+        ki = k_cache[a.to(q.device), r.to(q.device)].unsqueeze(0)
+        vi = v_cache[a.to(q.device), r.to(q.device)].unsqueeze(0)
+        sk = ki.shape[1]
+        mask = None
+        if local:
+            mask = local_mask(sq, sk, window_size[0], window_size[1])
+            if causal:
+                mask = mask | causal_mask_bottom_right(sq, sk)
+        elif causal:
+            mask = causal_mask_bottom_right(sq, sk)
+        bias = None
+        if alibi_slopes is not None:
+            sl = alibi_slopes if alibi_slopes.dim() == 1 else alibi_slopes[i]
+            bias = alibi_bias(sl, sq, sk).to(q.device)
+        o, l = attention_masked_ref(q[i:i + 1], ki, vi, mask, softmax_scale, upcast=upcast, lse_empty=float("-inf"),
+                                    bias=bias, softcap=softcap)
+        outs.append(o)
+        lses.append(l)
+    return torch.cat(outs), torch.cat(lses), k_cache, v_cache

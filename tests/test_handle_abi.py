@@ -208,3 +208,82 @@ def test_handle_decode_split_and_combine(fa):
         pt, _ = orc.attention_masked_ref(q[i:i + 1], kc[i:i + 1, :n], vc[i:i + 1, :n], upcast=False, reorder_ops=True)
         check_2x("out", o[i:i + 1], ref, pt)
     hf.close()
+
+
+@pytest.mark.gpu
+def test_handle_softcap_fwd_bwd(fa):
+    """softcap through the fa3 handle (csrc/flash_attn_v3/flash_api.cu:42,235): forward and backward, dS carries 1 - tanh^2."""
+    from tests._util import check_2x
+    lib = capi.load()
+    torch.manual_seed(3)
+    b, s, h, hk, d, cap = 2, 200, 4, 2, 64, 8.0
+    dev = "cuda"
+    q, g = [torch.randn(b, s, h, d, device=dev, dtype=torch.bfloat16) * 2 for _ in range(2)]
+    k, v = [torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    o, dq = torch.empty_like(q), torch.empty_like(q)
+    dk, dv = torch.empty_like(k), torch.empty_like(v)
+    lse = torch.empty(b, h, s, device=dev, dtype=torch.float32)
+    stream = torch.cuda.current_stream().cuda_stream
+    common = dict(b=b, seqlen_q=s, seqlen_k=s, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d), is_bf16=True,
+                  is_causal=True, num_splits=1, softcap=cap, softmax_lse_ptr=lse)
+    hf = Handle(lib, "fa3", "fwd")
+    _set_qkvo(hf, q, k, v, o)
+    hf.set(**common)
+    hf.call("run_mha_fwd", stream)
+    hb = Handle(lib, "fa3", "bwd")
+    _set_qkvo(hb, q, k, v, o)
+    hb.set(**common)
+    for name, t in (("do", g), ("dq", dq), ("dk", dk), ("dv", dv)):
+        hb.set(**{f"{name}_ptr": t, f"{name}_batch_stride": t.stride(0), f"{name}_row_stride": t.stride(1),
+                  f"{name}_head_stride": t.stride(2)})
+    hb.call("run_mha_bwd", stream)
+    torch.cuda.synchronize()
+    mask = orc.causal_mask_bottom_right(s, s).to(dev)
+    ref = orc.attention_grads_ref(q, k, v, g, mask, softcap=cap)
+    pt = orc.attention_grads_ref(q, k, v, g, mask, upcast=False, reorder_ops=True, softcap=cap)
+    for name, got, i in (("out", o, 0), ("dq", dq, 2), ("dk", dk, 3), ("dv", dv, 4)):
+        check_2x(name, got, ref[i], pt[i], atol=1e-3)
+    hf.close(); hb.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rotary", [False, True])
+def test_handle_paged_append_decode(fa, rotary):
+    """page_table + knew / vnew (+ rotary) through the fa3 handle: append into the pages, then decode over them."""
+    from tests._util import check_2x
+    lib = capi.load()
+    torch.manual_seed(4)
+    b, h, hk, d, page, per = 2, 8, 2, 128, 64, 5
+    dev, dt = "cuda", torch.bfloat16
+    n_pages = b * per + 2
+    pool_k = torch.randn(n_pages, page, hk, d, device=dev, dtype=dt)
+    pool_v = torch.randn_like(pool_k)
+    table = torch.randperm(n_pages)[: b * per].view(b, per).to(torch.int32).to(dev)
+    q = torch.randn(b, 1, h, d, device=dev, dtype=dt)
+    kn, vn = torch.randn(b, 1, hk, d, device=dev, dtype=dt), torch.randn(b, 1, hk, d, device=dev, dtype=dt)
+    used = torch.tensor([255, 64], device=dev, dtype=torch.int32)
+    o = torch.empty_like(q)
+    lse = torch.empty(b, h, 1, device=dev, dtype=torch.float32)
+    kw = {}
+    if rotary:
+        ang = torch.rand(per * page, 32, device=dev) * 6.28
+        kw = dict(rotary_cos=torch.cos(ang).to(dt), rotary_sin=torch.sin(ang).to(dt), rotary_interleaved=False)
+    ref, _, kref, vref = orc.kvcache_ref(q, pool_k, pool_v, k=kn, v=vn, cache_seqlens=used, block_table=table,
+                                         causal=True, **kw)
+    pt, _, _, _ = orc.kvcache_ref(q, pool_k, pool_v, k=kn, v=vn, cache_seqlens=used, block_table=table, causal=True,
+                                  upcast=False, **kw)
+    hf = Handle(lib, "fa3", "fwd")
+    _set_qkvo(hf, q, pool_k, pool_v, o)
+    hf.set(b=b, seqlen_q=1, seqlen_k=per * page, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d), is_bf16=True,
+           is_causal=True, seqused_k=used, softmax_lse_ptr=lse, num_splits=1, page_table=table,
+           page_table_batch_stride=table.stride(0), page_size=page, num_pages=n_pages, knew_ptr=kn, vnew_ptr=vn,
+           seqlen_knew=1, knew_batch_stride=kn.stride(0), knew_row_stride=kn.stride(1), knew_head_stride=kn.stride(2),
+           vnew_batch_stride=vn.stride(0), vnew_row_stride=vn.stride(1), vnew_head_stride=vn.stride(2))
+    if rotary:
+        hf.set(rotary_cos_ptr=kw["rotary_cos"], rotary_sin_ptr=kw["rotary_sin"], rotary_dim=64, is_rotary_interleaved=False)
+    hf.call("run_mha_fwd", torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert torch.equal(pool_v, vref)
+    torch.testing.assert_close(pool_k.float(), kref.float(), atol=2e-2, rtol=8e-3)
+    check_2x("out", o, ref, pt, atol=2e-3)
+    hf.close()

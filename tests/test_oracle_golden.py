@@ -9,7 +9,9 @@ import torch
 
 from oracle import attention_oracle as orc
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+_ALL = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = [p for p in _ALL if not os.path.basename(p).startswith("rotary_")]
+GOLDEN_ROTARY = [p for p in _ALL if os.path.basename(p).startswith("rotary_")]
 
 
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
@@ -70,3 +72,59 @@ def test_flop_convention():
     # benchmarks/benchmark_flash_attention.py:27-30
     assert orc.attention_flops(8, 2048, 2048, 16, 128, False, "fwd") == 4 * 8 * 2048 * 2048 * 16 * 128
     assert orc.attention_flops(1, 8192, 8192, 32, 128, True, "fwd_bwd") == 3.5 * 4 * 8192 * 8192 * 32 * 128 // 2
+
+
+@pytest.mark.parametrize("path", GOLDEN_ROTARY, ids=[os.path.basename(p)[:-4] for p in GOLDEN_ROTARY])
+def test_rotary_oracle_matches_reference_golden(path):
+    """rotary_ref against the reference's apply_rotary_emb_torch (flash_attn/layers/rotary.py:22-32), positions 0..s-1,
+    and with an offset: rotating rows at positions o..o+s-1 equals the golden of the shifted table."""
+    g = np.load(path)
+    x, cos, sin = [torch.from_numpy(g[n]) for n in ("x", "cos", "sin")]
+    b, s = x.shape[:2]
+    pos = torch.arange(s).view(1, s).expand(b, s)
+    out = orc.rotary_ref(x, cos, sin, pos, interleaved=bool(g["interleaved"]))
+    np.testing.assert_allclose(out.numpy(), g["out"], rtol=1e-5, atol=1e-6)
+    half = s // 2    # second half of the rows alone, at offset `half`
+    out2 = orc.rotary_ref(x[:, half:], cos, sin, pos[:, half:], interleaved=bool(g["interleaved"]))
+    np.testing.assert_allclose(out2.numpy(), g["out"][:, half:], rtol=1e-5, atol=1e-6)
+
+
+def test_kvcache_ref_reduces_to_plain_attention():
+    """kvcache_ref with no extras is attention over the first cache_seqlens keys; paged / batch-idx / leftpad
+    addressing returns the same numbers as the equivalent contiguous cache."""
+    torch.manual_seed(0)
+    b, sq, h, hk, d, sk = 3, 2, 4, 2, 32, 64
+    q = torch.randn(b, sq, h, d)
+    kc, vc = torch.randn(b, sk, hk, d), torch.randn(b, sk, hk, d)
+    lens = torch.tensor([64, 17, 40], dtype=torch.int32)
+    out, lse, _, _ = orc.kvcache_ref(q, kc, vc, cache_seqlens=lens, causal=True)
+    for i in range(b):
+        n = int(lens[i])
+        o_i, l_i = orc.attention_masked_ref(q[i:i + 1], kc[i:i + 1, :n], vc[i:i + 1, :n],
+                                            orc.causal_mask_bottom_right(sq, n), lse_empty=float("-inf"))
+        np.testing.assert_allclose(out[i:i + 1].numpy(), o_i.numpy(), rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(lse[i:i + 1].numpy(), l_i.numpy(), rtol=1e-6, atol=1e-6)
+    # paged: 16-row pages in a shuffled pool
+    ps = 16
+    perm = torch.randperm(b * sk // ps)
+    table = perm.view(b, sk // ps).to(torch.int32)
+    pool_k, pool_v = torch.empty(b * sk // ps, ps, hk, d), torch.empty(b * sk // ps, ps, hk, d)
+    pool_k[perm] = kc.view(b * sk // ps, ps, hk, d)
+    pool_v[perm] = vc.view(b * sk // ps, ps, hk, d)
+    out_p, lse_p, _, _ = orc.kvcache_ref(q, pool_k, pool_v, cache_seqlens=lens, block_table=table, causal=True)
+    np.testing.assert_allclose(out_p.numpy(), out.numpy(), rtol=1e-6, atol=1e-6)
+    # cache_batch_idx: reversed cache rows
+    idx = torch.tensor([2, 1, 0], dtype=torch.int32)
+    out_i, _, _, _ = orc.kvcache_ref(q, kc.flip(0), vc.flip(0), cache_seqlens=lens, cache_batch_idx=idx, causal=True)
+    np.testing.assert_allclose(out_i.numpy(), out.numpy(), rtol=1e-6, atol=1e-6)
+    # leftpad: shift the valid keys right by 5
+    lp = torch.tensor([0, 5, 3], dtype=torch.int32)
+    kc2, vc2 = torch.randn(b, sk + 8, hk, d), torch.randn(b, sk + 8, hk, d)
+    lens2 = lens.clone()
+    for i in range(b):
+        n, o = int(lens[i]), int(lp[i])
+        n = min(n, sk + 8 - o)
+        kc2[i, o:o + n], vc2[i, o:o + n] = kc[i, :n], vc[i, :n]
+        lens2[i] = o + n
+    out_l, _, _, _ = orc.kvcache_ref(q, kc2, vc2, cache_seqlens=lens2, cache_leftpad=lp, causal=True)
+    np.testing.assert_allclose(out_l.numpy(), out.numpy(), rtol=1e-6, atol=1e-6)

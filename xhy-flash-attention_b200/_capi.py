@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
 LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
-FA_B200_ABI_VERSION = 2
+FA_B200_ABI_VERSION = 3
 
 
 class Tensor(C.Structure):
@@ -48,6 +48,11 @@ class Params(C.Structure):
         ("p_dropout", C.c_float), ("philox_seed", C.c_uint64), ("philox_offset", C.c_uint64), ("s_dmask", C.c_void_p),
         ("attn_mask", C.c_void_p), ("mask_head_mod", C.c_int32), ("mask_seq_mod", C.c_int32),
         ("unscale_softmax", C.c_float),
+        ("page_table", C.c_void_p), ("page_table_batch_stride", C.c_int64),
+        ("page_size", C.c_int32), ("num_pages", C.c_int32),
+        ("kv_batch_idx", C.c_void_p), ("b_k", C.c_int32),
+        ("leftpad_k", C.c_void_p), ("softcap", C.c_float),
+        ("alibi_slopes", C.c_void_p), ("alibi_batch_stride", C.c_int64),
     ]
 
 
@@ -77,6 +82,10 @@ def load() -> C.CDLL:
     lib.fa_b200_decode_num_splits.restype = C.c_int
     lib.fa_b200_append_kv.argtypes = ([C.c_void_p] * 5 + [C.c_int] * 6 + [C.c_int64] * 6 + [C.c_void_p])
     lib.fa_b200_append_kv.restype = C.c_bool
+    lib.fa_b200_append_kv_paged.argtypes = [C.POINTER(Params), C.c_void_p, C.c_void_p, C.c_int] + [C.c_int64] * 3 + [C.c_void_p]
+    lib.fa_b200_append_kv_paged.restype = C.c_bool
+    lib.fa_b200_rotary.argtypes = [C.c_void_p] * 5 + [C.c_int] * 9 + [C.c_int64] * 6 + [C.c_void_p]
+    lib.fa_b200_rotary.restype = C.c_bool
     lib.fa_b200_lse_merge.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int,
                                                          C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p])
     lib.fa_b200_lse_merge.restype = C.c_bool

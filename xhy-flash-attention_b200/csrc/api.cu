@@ -62,6 +62,12 @@ static void check_common(const Params &p) {
   FA_CHECK(p.q.ptr && p.k.ptr && p.v.ptr, "q, k, v must be set");
   FA_CHECK(device_cc_major() >= 10, "libflashattn_b200 needs a Blackwell (sm_100a) device");
   if (p.attn_mask) FA_CHECK(p.mask_head_mod > 0 && p.mask_seq_mod > 0, "attn_mask needs mask_head_mod and mask_seq_mod");
+  FA_CHECK(p.softcap >= 0.f, "softcap must be >= 0");
+  if (p.page_table) {
+    FA_CHECK(p.page_size > 0 && p.num_pages > 0 && p.page_table_batch_stride > 0, "page_table needs page_size, num_pages and its batch stride");
+    FA_CHECK(!p.kv_batch_idx, "page_table and kv_batch_idx are exclusive");
+    FA_CHECK(!p.cu_seqlens_k, "page_table with cu_seqlens_k is not supported");
+  }
   if (p.lt_start) {
     FA_CHECK(p.h_mask > 0 && p.h % p.h_mask == 0, "flashmask heads must divide num_heads");
   } else {
@@ -75,7 +81,10 @@ void run_fwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   // dropout / return_softmax take the generic kernels (Philox per element); the tcgen05 kernels are dropout-free
-  const bool special = p.p_dropout > 0.f || p.s_dmask != nullptr || p.attn_mask != nullptr;
+  // so do softcap / ALiBi and the KV-cache addressing modes outside the decode kernel (inference features)
+  const bool special = p.p_dropout > 0.f || p.s_dmask != nullptr || p.attn_mask != nullptr || p.softcap > 0.f ||
+                       p.alibi_slopes != nullptr || p.page_table != nullptr || p.kv_batch_idx != nullptr ||
+                       p.leftpad_k != nullptr;
   if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
   else generic_fwd(p, s);
 }
@@ -86,7 +95,9 @@ void run_bwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.softmax_d, "softmax_d workspace must be set");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
-  if (!p.force_generic && !(p.p_dropout > 0.f) && p.attn_mask == nullptr && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
+  FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
+  const bool special = p.p_dropout > 0.f || p.attn_mask != nullptr || p.softcap > 0.f || p.alibi_slopes != nullptr;
+  if (!p.force_generic && !special && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }
 
@@ -236,6 +247,29 @@ bool fa_b200_flashmask_prepare(const fa_b200_params *p, int block_n, cudaStream_
   FA_BEGIN
   FA_CHECK(p && p->lt_start && p->flashmask_maxmin, "flashmask_prepare needs lt_start and the maxmin workspace");
   fa::flashmask_prepare(*p, block_n, stream);
+  FA_END
+}
+
+bool fa_b200_append_kv_paged(const fa_b200_params *p, const void *k_new, const void *v_new, int seqlen_new,
+                             int64_t new_batch_stride, int64_t new_row_stride, int64_t new_head_stride,
+                             cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p && p->abi_version == FA_B200_ABI_VERSION, "fa_b200_params.abi_version mismatch");
+  FA_CHECK(k_new && v_new && p->k.ptr && p->v.ptr, "append_kv: null tensor");
+  fa::append_kv_paged(*p, k_new, v_new, seqlen_new, new_batch_stride, new_row_stride, new_head_stride, stream);
+  FA_END
+}
+
+bool fa_b200_rotary(const void *x, void *out, const void *cos, const void *sin, const int32_t *seqlen_offsets,
+                    int batch, int seqlen, int num_heads, int head_size, int rotary_dim, int seqlen_ro,
+                    int interleaved, int fixed_position, int is_bf16,
+                    int64_t x_batch_stride, int64_t x_row_stride, int64_t x_head_stride,
+                    int64_t out_batch_stride, int64_t out_row_stride, int64_t out_head_stride, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(x && out && cos && sin, "rotary: null tensor");
+  fa::rotary(x, out, cos, sin, seqlen_offsets, batch, seqlen, num_heads, head_size, rotary_dim, seqlen_ro, interleaved,
+             fixed_position, is_bf16, x_batch_stride, x_row_stride, x_head_stride, out_batch_stride, out_row_stride,
+             out_head_stride, stream);
   FA_END
 }
 

@@ -1,5 +1,5 @@
 // aux_kernels.cu -- the HBM-bound helper kernels: split-KV LSE combine, FlashMask block min/max scan,
-// KV-cache append, ring-attention LSE merge.
+// KV-cache append (contiguous / paged), rotary embedding, ring-attention LSE merge.
 #include <climits>
 #include <math_constants.h>
 
@@ -156,6 +156,63 @@ append_kv_kernel(const uint4 *k_new, const uint4 *v_new, uint4 *k_cache, uint4 *
   }
 }
 
+// Append for every cache layout fa_b200_params can describe: contiguous, kv_batch_idx-indirected, paged
+// (csrc/flash_attn_v3/paged_kv.h store_K / store_V).  Row r of batch element bi lands at physical row
+// seqused_k[bi] + r; K and V may have different strides, so one launch handles one tensor.
+__global__ void __launch_bounds__(256)
+append_paged_kernel(const uint4 *src, uint4 *cache, const int32_t *cache_seqlens, const int32_t *page_table,
+                    int64_t table_stride, int page_size, const int32_t *kv_batch_idx, int batch, int seqlen_new,
+                    int seqlen_cache, int h_k, int d8, int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs,
+                    int64_t chs) {
+  const int64_t total = (int64_t)batch * seqlen_new * h_k * d8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = i % d8;
+    const int hh = (i / d8) % h_k;
+    const int r = (i / ((int64_t)d8 * h_k)) % seqlen_new;
+    const int bi = i / ((int64_t)d8 * h_k * seqlen_new);
+    const int dst_row = (cache_seqlens ? cache_seqlens[bi] : 0) + r;
+    if (dst_row >= seqlen_cache) continue;
+    int64_t slab = kv_batch_idx ? kv_batch_idx[bi] : bi, row = dst_row;
+    if (page_table) {
+      slab = page_table[(int64_t)bi * table_stride + dst_row / page_size];
+      row = dst_row % page_size;
+    }
+    cache[(slab * cbs + row * crs + (int64_t)hh * chs) / 8 + c] = src[(bi * nbs + (int64_t)r * nrs + (int64_t)hh * nhs) / 8 + c];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Rotary embedding, out of place (csrc/flash_attn_v3/rotary.h: interleaved pairs (2j, 2j+1), contiguous pairs
+// (j, j + rotary_dim/2); x1' = x1 cos - x2 sin, x2' = x1 sin + x2 cos in fp32, one rounding; position of row r of batch
+// element bi = seqlen_offsets[bi] + (fixed_position ? 0 : r), as flash_attn_with_kvcache rotates q and k_new).
+// One thread per (batch, row, head, pair-or-tail-element).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+rotary_kernel(const T *x, T *out, const T *cosp, const T *sinp, const int32_t *offsets, int batch, int seqlen, int heads,
+              int d, int rdim, int seqlen_ro, int interleaved, int fixed, int64_t xbs, int64_t xrs, int64_t xhs,
+              int64_t obs, int64_t ors, int64_t ohs) {
+  const int half = rdim / 2;
+  const int per_head = half + (d - rdim);                     // rotated pairs + copied tail elements
+  const int64_t total = (int64_t)batch * seqlen * heads * per_head;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int j = i % per_head;
+    const int hh = (i / per_head) % heads;
+    const int r = (i / ((int64_t)per_head * heads)) % seqlen;
+    const int bi = i / ((int64_t)per_head * heads * seqlen);
+    const T *xi = x + bi * xbs + (int64_t)r * xrs + (int64_t)hh * xhs;
+    T *oi = out + bi * obs + (int64_t)r * ors + (int64_t)hh * ohs;
+    if (j >= half) { oi[rdim + (j - half)] = xi[rdim + (j - half)]; continue; }
+    const int pos = (offsets ? offsets[bi] : 0) + (fixed ? 0 : r);
+    const int e1 = interleaved ? 2 * j : j, e2 = interleaved ? 2 * j + 1 : j + half;
+    const float x1 = to_f(xi[e1]), x2 = to_f(xi[e2]);
+    float c = 1.f, sn = 0.f;                                  // positions past the table are left unrotated
+    if (pos < seqlen_ro) { c = to_f(cosp[(int64_t)pos * half + j]); sn = to_f(sinp[(int64_t)pos * half + j]); }
+    oi[e1] = from_f<T>(x1 * c - x2 * sn);
+    oi[e2] = from_f<T>(x1 * sn + x2 * c);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // ring-attention step merge (same algebra as the combine): treats +inf and -inf LSE as "no contribution".
 // One warp per (row, head); o contiguous (rows, heads, d).
@@ -231,6 +288,51 @@ void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cach
   append_kv_kernel<<<blocks, 256, 0, s>>>((const uint4 *)k_new, (const uint4 *)v_new, (uint4 *)k_cache, (uint4 *)v_cache,
                                          cache_seqlens, batch, seqlen_new, seqlen_cache, h_k, d / 8, nbs, nrs, nhs, cbs,
                                          crs, chs);
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void append_kv_paged(const Params &p, const void *k_new, const void *v_new, int seqlen_new, int64_t nbs, int64_t nrs,
+                     int64_t nhs, cudaStream_t s) {
+  FA_CHECK(nbs % 8 == 0 && nrs % 8 == 0 && nhs % 8 == 0, "append_kv: strides must be multiples of 8 elements");
+  FA_CHECK(p.d % 8 == 0, "append_kv: head_size must be a multiple of 8");
+  FA_CHECK(!(p.page_table && p.kv_batch_idx), "append_kv: page_table and kv_batch_idx are exclusive");
+  FA_CHECK(!p.page_table || p.page_size > 0, "append_kv: page_size");
+  const int64_t total = (int64_t)p.b * seqlen_new * p.h_k * (p.d / 8);
+  int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+  if (blocks < 1) blocks = 1;
+  const fa_b200_tensor *ts[2] = {&p.k, &p.v};
+  const void *src[2] = {k_new, v_new};
+  for (int i = 0; i < 2; ++i) {
+    const fa_b200_tensor &t = *ts[i];
+    FA_CHECK(t.batch_stride % 8 == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0,
+             "append_kv: cache strides must be multiples of 8 elements");
+    FA_CHECK(((uintptr_t)t.ptr | (uintptr_t)src[i]) % 16 == 0, "append_kv: tensors must be 16-byte aligned");
+    append_paged_kernel<<<blocks, 256, 0, s>>>((const uint4 *)src[i], (uint4 *)t.ptr, p.seqused_k, p.page_table,
+                                               p.page_table_batch_stride, p.page_size, p.kv_batch_idx, p.b, seqlen_new,
+                                               p.seqlen_k, p.h_k, p.d / 8, nbs, nrs, nhs, t.batch_stride, t.row_stride,
+                                               t.head_stride);
+    FA_CUDA(cudaGetLastError());
+    note_launch(1);
+  }
+}
+
+void rotary(const void *x, void *out, const void *cosp, const void *sinp, const int32_t *offsets, int batch, int seqlen,
+            int heads, int d, int rdim, int seqlen_ro, int interleaved, int fixed, int is_bf16, int64_t xbs, int64_t xrs,
+            int64_t xhs, int64_t obs, int64_t ors, int64_t ohs, cudaStream_t s) {
+  FA_CHECK(rdim >= 0 && rdim <= d && rdim % 2 == 0, "rotary: rotary_dim must be even and <= head_size");
+  const int64_t total = (int64_t)batch * seqlen * heads * (rdim / 2 + d - rdim);
+  int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+  if (blocks < 1) blocks = 1;
+  if (is_bf16)
+    rotary_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>((const __nv_bfloat16 *)x, (__nv_bfloat16 *)out,
+                                                        (const __nv_bfloat16 *)cosp, (const __nv_bfloat16 *)sinp, offsets,
+                                                        batch, seqlen, heads, d, rdim, seqlen_ro, interleaved, fixed, xbs,
+                                                        xrs, xhs, obs, ors, ohs);
+  else
+    rotary_kernel<__half><<<blocks, 256, 0, s>>>((const __half *)x, (__half *)out, (const __half *)cosp,
+                                                 (const __half *)sinp, offsets, batch, seqlen, heads, d, rdim, seqlen_ro,
+                                                 interleaved, fixed, xbs, xrs, xhs, obs, ors, ohs);
   FA_CUDA(cudaGetLastError());
   note_launch(1);
 }

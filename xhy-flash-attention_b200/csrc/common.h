@@ -63,6 +63,11 @@ void flashmask_prepare(const Params &p, int block_n, cudaStream_t s, bool with_l
 void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,
                int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16,
                int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s);
+void append_kv_paged(const Params &p, const void *k_new, const void *v_new, int seqlen_new, int64_t nbs, int64_t nrs,
+                     int64_t nhs, cudaStream_t s);
+void rotary(const void *x, void *out, const void *cosp, const void *sinp, const int32_t *offsets, int batch, int seqlen,
+            int heads, int d, int rdim, int seqlen_ro, int interleaved, int fixed, int is_bf16, int64_t xbs, int64_t xrs,
+            int64_t xhs, int64_t obs, int64_t ors, int64_t ohs, cudaStream_t s);
 void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
                int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride, int64_t step_row_stride,
                int64_t step_head_stride, cudaStream_t s);

@@ -50,6 +50,11 @@ template <int HD> struct DecSmem {
   static_assert(kMergeBytes <= 2 * kDStages * kTile, "merge scratch must fit in the ring");
 };
 
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float ex2d(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -105,7 +110,10 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   const int g = p.h / p.h_k;
   const int sq = p.seqlen_q;
   const int G = sq * g;                                       // packed rows in use (<= 16)
-  const int sk = p.seqused_k ? min(p.seqused_k[bi], p.seqlen_k) : p.seqlen_k;
+  // valid keys are the physical cache rows [leftpad, leftpad + sk) (csrc/flash_attn_v3/seqlen.h:73-80); everything
+  // below the mask intervals works on PHYSICAL rows so that 64-key tiles never straddle a page
+  const int leftpad = p.leftpad_k ? p.leftpad_k[bi] : 0;
+  const int sk = max((p.seqused_k ? min(p.seqused_k[bi], p.seqlen_k) : p.seqlen_k) - leftpad, 0);
 
   auto full_bar = [&](int s) { return sbase + L::kBar + s * 8; };
   auto empty_bar = [&](int s) { return sbase + L::kBar + (kDStages + s) * 8; };
@@ -127,7 +135,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   for (int qi = 0; qi < sq; ++qi) {
     int lo, hi;
     row_interval(p, qi, sq, sk, split_lo, split_hi, lo, hi);
-    if (hi > lo) { cta_lo = min(cta_lo, lo); cta_hi = max(cta_hi, hi); }
+    if (hi > lo) { cta_lo = min(cta_lo, lo + leftpad); cta_hi = max(cta_hi, hi + leftpad); }
   }
   const int t_lo = cta_hi > cta_lo ? cta_lo / kDT : 0;
   const int t_hi = cta_hi > cta_lo ? ceil_div(cta_hi, kDT) : 0;
@@ -137,15 +145,24 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   if (warp == kDWarps) {
     // ======================= TMA producer =======================
     if (lane == 0) {
+      const int32_t *table = p.page_table ? p.page_table + (int64_t)bi * p.page_table_batch_stride : nullptr;
+      const int bkv = p.kv_batch_idx ? p.kv_batch_idx[bi] : bi;
+      // paged cache: the page index of tile it+1 is fetched while waiting for the slot of tile it
+      int page_next = (table && n_tiles > 0) ? table[(t_lo * kDT) / p.page_size] : 0;
       for (int it = 0; it < n_tiles; ++it) {
         const int st = it % kDStages;
+        int row = (t_lo + it) * kDT, slab = bkv;
+        if (table) {
+          slab = page_next;
+          row -= (row / p.page_size) * p.page_size;
+          if (it + 1 < n_tiles) page_next = table[((t_lo + it + 1) * kDT) / p.page_size];
+        }
         mbar_wait(empty_bar(st), ((it / kDStages) & 1) ^ 1);
         mbar_expect_tx(full_bar(st), 2 * L::kTile);
-        const int row = (t_lo + it) * kDT;
 #pragma unroll
         for (int hf = 0; hf < kHalves; ++hf) {
-          tma_load_4d(sbase + L::kK + st * L::kTile + hf * (kDT * 128), &tm.k, full_bar(st), hf * 64, hk, row, bi);
-          tma_load_4d(sbase + L::kV + st * L::kTile + hf * (kDT * 128), &tm.v, full_bar(st), hf * 64, hk, row, bi);
+          tma_load_4d(sbase + L::kK + st * L::kTile + hf * (kDT * 128), &tm.k, full_bar(st), hf * 64, hk, row, slab);
+          tma_load_4d(sbase + L::kV + st * L::kTile + hf * (kDT * 128), &tm.v, full_bar(st), hf * 64, hk, row, slab);
         }
       }
     }
@@ -171,10 +188,22 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
     }
   }
   int loA = 0, hiA = 0, loB = 0, hiB = 0;
-  if (rA < G) row_interval(p, rA / g, sq, sk, split_lo, split_hi, loA, hiA);
-  if (rB < G) row_interval(p, rB / g, sq, sk, split_lo, split_hi, loB, hiB);
+  if (rA < G) { row_interval(p, rA / g, sq, sk, split_lo, split_hi, loA, hiA); loA += leftpad; hiA += leftpad; }
+  if (rB < G) { row_interval(p, rB / g, sq, sk, split_lo, split_hi, loB, hiB); loB += leftpad; hiB += leftpad; }
+  const int kv_end = leftpad + sk;
 
-  const float scale_log2 = p.softmax_scale * kLog2e;
+  // softcap: logits = softcap * tanh(scale * s / softcap) (csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:537-556);
+  // ALiBi: logits -= slope * |key - (query + sk - sq)|, per packed row
+  const bool has_cap = p.softcap > 0.f, has_alibi = p.alibi_slopes != nullptr;
+  const float scale_log2 = has_cap ? p.softcap * kLog2e : p.softmax_scale * kLog2e;
+  const float pre_cap = has_cap ? p.softmax_scale / p.softcap : 0.f;
+  float slopeA = 0.f, slopeB = 0.f;
+  int diagA = 0, diagB = 0;                                    // physical key on the (bottom-right) diagonal of the row
+  if (has_alibi) {
+    const float *sl = p.alibi_slopes + (int64_t)bi * p.alibi_batch_stride + hk * g;
+    if (rA < G) { slopeA = sl[rA % g] * kLog2e; diagA = rA / g + sk - sq + leftpad; }
+    if (rB < G) { slopeB = sl[rB % g] * kLog2e; diagB = rB / g + sk - sq + leftpad; }
+  }
   float mA = -CUDART_INF_F, mB = -CUDART_INF_F, lA = 0.f, lB = 0.f;
   float o[HD / 8][4];
 #pragma unroll
@@ -191,12 +220,12 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
     const int c0 = (t_lo + it) * kDT;
     mbar_wait(full_bar(st), (it / kDStages) & 1);
     bool touched = false;
-    if (c0 + kDT > sk) {
+    if (c0 + kDT > kv_end || c0 < leftpad) {
       // cache rows at or beyond the used length hold arbitrary bits (possibly NaN): zero this warp's V rows so that
       // P = 0 times garbage cannot poison O (the reference zero-fills the V tail: flash_fwd_kernel.h:346-349)
       for (int i = lane; i < 16 * (HD / 8); i += 32) {
         const int key = warp * 16 + i / (HD / 8), chunk = i % (HD / 8);
-        if (c0 + key >= sk) sts128(vb + tile_off(key, chunk), 0u, 0u, 0u, 0u);
+        if (c0 + key >= kv_end || c0 + key < leftpad) sts128(vb + tile_off(key, chunk), 0u, 0u, 0u, 0u);
       }
       __syncwarp();
       touched = true;
@@ -211,6 +240,12 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
       mma16816<kBf16>(s[0], qa[ks], r0, r1);
       mma16816<kBf16>(s[1], qa[ks], r2, r3);
     }
+    if (has_cap) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s[j][e] = tanh_fast(s[j][e] * pre_cap);
+    }
     // mask + online softmax (log2 domain)
     float mxA = -CUDART_INF_F, mxB = -CUDART_INF_F;
 #pragma unroll
@@ -218,8 +253,13 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int key = c0 + warp * 16 + j * 8 + 2 * quad + e;
-        s[j][e] = (key >= loA && key < hiA) ? s[j][e] * scale_log2 : -CUDART_INF_F;
-        s[j][2 + e] = (key >= loB && key < hiB) ? s[j][2 + e] * scale_log2 : -CUDART_INF_F;
+        float a = s[j][e] * scale_log2, b2 = s[j][2 + e] * scale_log2;
+        if (has_alibi) {
+          a -= slopeA * fabsf((float)(key - diagA));
+          b2 -= slopeB * fabsf((float)(key - diagB));
+        }
+        s[j][e] = (key >= loA && key < hiA) ? a : -CUDART_INF_F;
+        s[j][2 + e] = (key >= loB && key < hiB) ? b2 : -CUDART_INF_F;
         mxA = fmaxf(mxA, s[j][e]);
         mxB = fmaxf(mxB, s[j][2 + e]);
       }
@@ -349,8 +389,11 @@ bool kv_ok(const fa_b200_tensor &t, int heads, int batch) {
 template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s) {
   using L = DecSmem<HD>;
   DecTma tm;
-  tm.k = make_tma_4d(kv_desc(p.k, p.d, p.h_k, p.seqlen_k, p.b));
-  tm.v = make_tma_4d(kv_desc(p.v, p.d, p.h_k, p.seqlen_k, p.b));
+  // contiguous cache: (d, h_k, seqlen_k, cache batch); paged: (d, h_k, page_size, num_pages)
+  const int64_t rows = p.page_table ? p.page_size : p.seqlen_k;
+  const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
+  tm.k = make_tma_4d(kv_desc(p.k, p.d, p.h_k, rows, slabs));
+  tm.v = make_tma_4d(kv_desc(p.v, p.d, p.h_k, rows, slabs));
   auto kern = decode_kernel<HD, kBf16>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -370,7 +413,9 @@ bool decode_supported(const Params &p) {
   if (p.d != 64 && p.d != 128) return false;
   if (p.cu_seqlens_q || p.cu_seqlens_k || p.lt_start) return false;
   if (p.seqlen_q * (p.h / p.h_k) > kDRows) return false;
-  if (!kv_ok(p.k, p.h_k, p.b) || !kv_ok(p.v, p.h_k, p.b)) return false;
+  if (p.page_table && (p.page_size <= 0 || p.page_size % kDT != 0 || p.num_pages <= 0)) return false;
+  const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
+  if (!kv_ok(p.k, p.h_k, slabs) || !kv_ok(p.v, p.h_k, slabs)) return false;
   if (((uintptr_t)p.q.ptr & 3) != 0 || p.q.row_stride % 2 != 0 || p.q.head_stride % 2 != 0 || p.q.batch_stride % 2 != 0)
     return false;
   if (p.num_splits > 1) return ((uintptr_t)p.oaccum & 15) == 0;

@@ -80,12 +80,52 @@ __device__ __forceinline__ Seq get_seq(const Params &p, int bi) {
   bool qb, kb;
   seq_bounds(p, bi, s.q_row0, s.sq, s.k_row0, s.sk, qb, kb);
   s.q_boff = qb ? bi : 0;
-  s.k_boff = kb ? bi : 0;
+  s.k_boff = kb ? (p.kv_batch_idx ? p.kv_batch_idx[bi] : bi) : 0;
+  if (p.leftpad_k) {                       // valid keys are [leftpad, seqused) (csrc/flash_attn_v3/seqlen.h:73-80)
+    const int lp = p.leftpad_k[bi];
+    s.k_row0 += lp;
+    s.sk = max(s.sk - lp, 0);
+  }
   return s;
 }
 
 __device__ __forceinline__ int64_t elem_off(const fa_b200_tensor &t, int64_t boff, int64_t row, int head) {
   return boff * t.batch_stride + row * t.row_stride + (int64_t)head * t.head_stride;
+}
+
+// K/V row of key `col` of batch element bi: contiguous cache or paged (csrc/flash_attn_v3/paged_kv.h)
+template <typename T>
+__device__ __forceinline__ const T *kv_row(const Params &p, const fa_b200_tensor &t, const Seq &s, int bi, int hk, int col) {
+  const int64_t r = (int64_t)s.k_row0 + col;
+  if (p.page_table) {
+    const int page = p.page_table[(int64_t)bi * p.page_table_batch_stride + r / p.page_size];
+    return (const T *)t.ptr + (int64_t)page * t.batch_stride + (r % p.page_size) * t.row_stride + (int64_t)hk * t.head_stride;
+  }
+  return (const T *)t.ptr + s.k_boff * t.batch_stride + r * t.row_stride + (int64_t)hk * t.head_stride;
+}
+
+// logit in the log2 domain from the raw dot product (+ dense-mask term): scale, softcap (tanh, before masks and ALiBi:
+// csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:537-556,1064-1067), ALiBi.  *dfac = d logit / d (scale * dot).
+struct LogitCtx {
+  float scale, scale_log2, softcap, slope;
+  int shift;
+  bool plain;
+};
+__device__ __forceinline__ LogitCtx make_logit_ctx(const Params &p, int bi, int hq, int shift) {
+  LogitCtx c;
+  c.scale = p.softmax_scale; c.scale_log2 = p.softmax_scale * kLog2e; c.softcap = p.softcap;
+  c.slope = p.alibi_slopes ? p.alibi_slopes[(int64_t)bi * p.alibi_batch_stride + hq] : 0.f;
+  c.shift = shift;
+  c.plain = !(p.softcap > 0.f) && p.alibi_slopes == nullptr;
+  return c;
+}
+__device__ __forceinline__ float logit2(const LogitCtx &c, float dot, int row, int col, float *dfac = nullptr) {
+  if (c.plain) { if (dfac) *dfac = 1.f; return dot * c.scale_log2; }
+  float x = dot * c.scale, f = 1.f;
+  if (c.softcap > 0.f) { const float t = tanhf(x / c.softcap); x = c.softcap * t; f = 1.f - t * t; }
+  x -= c.slope * fabsf((float)(col - (row + c.shift)));
+  if (dfac) *dfac = f;
+  return x * kLog2e;
 }
 
 // column range [lo, hi) that causal / window / split leave open for a query row
@@ -123,7 +163,7 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
   for (int e = lane; e < d; e += 32) q_s[warp][e] = to_f(q[e]);
   __syncwarp();
 
-  const float scale_log2 = p.softmax_scale * kLog2e;
+  const LogitCtx lc = make_logit_ctx(p, bi, hq, sq_.sk - sq_.sq);
   int lo, hi;
   col_range(p, m, row, split, lo, hi);
 
@@ -135,14 +175,11 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
   const DropCtx dc = make_drop_ctx(p, bi, hq, row);
   const float rp = drop ? 1.f / (1.f - p.p_dropout) : 1.f;
 
-  const T *kbase = (const T *)p.k.ptr + elem_off(p.k, sq_.k_boff, sq_.k_row0, hk);
-  const T *vbase = (const T *)p.v.ptr + elem_off(p.v, sq_.k_boff, sq_.k_row0, hk);
-
   for (int j0 = lo; j0 < hi; j0 += 32) {
     const int col = j0 + lane;
     float s = -CUDART_INF_F;
     if (col < hi && !is_masked(m, row, col))
-      s = (dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) * scale_log2;
+      s = logit2(lc, dot_row(q_s[warp], kv_row<T>(p, p.k, sq_, bi, hk, col), d) + mask_term<T>(p, bi, hq, row, col), row, col);
     const float mnew = fmaxf(mx, warp_max(s));
     if (mnew == -CUDART_INF_F) continue;  // nothing visible so far (warp-uniform)
     const float corr = exp2f(mx - mnew);  // mx = -inf -> 0
@@ -156,7 +193,7 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
     for (int jj = 0; jj < nj; ++jj) {
       const float pv = __shfl_sync(0xffffffffu, pj, jj);
       if (pv == 0.f) continue;  // warp-uniform
-      const T *vrow = vbase + (int64_t)(j0 + jj) * p.v.row_stride;
+      const T *vrow = kv_row<T>(p, p.v, sq_, bi, hk, j0 + jj);
 #pragma unroll
       for (int c = 0; c < kMaxC; ++c) {
         const int e = lane + 32 * c;
@@ -176,8 +213,8 @@ __global__ void __launch_bounds__(kWarps * 32) generic_fwd_kernel(const Params p
       const int col = j0 + lane;
       float pr = 0.f;
       if (!empty && col >= lo && col < hi && !is_masked(m, row, col)) {
-        pr = exp2f((dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
-                       scale_log2 - lse2);
+        pr = exp2f(logit2(lc, dot_row(q_s[warp], kv_row<T>(p, p.k, sq_, bi, hk, col), d) + mask_term<T>(p, bi, hq, row, col),
+                          row, col) - lse2);
         if (drop && !dropout_keep(dc, col)) pr = -pr;
       }
       if (col < p.seqlen_k_rounded) sd[col] = from_f<T>(pr);
@@ -244,7 +281,7 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
   const T *g = (const T *)p.dout.ptr + elem_off(p.dout, s_.q_boff, s_.q_row0 + row, hq);
   for (int e = lane; e < d; e += 32) { q_s[warp][e] = to_f(q[e]); g_s[warp][e] = to_f(g[e]); }
   __syncwarp();
-  const float scale_log2 = p.softmax_scale * kLog2e;
+  const LogitCtx lc = make_logit_ctx(p, bi, hq, s_.sk - s_.sq);
   const float lse = p.softmax_lse[((int64_t)bi * p.h + hq) * p.seqlen_q + row];
   const float dsum = p.softmax_d[((int64_t)bi * p.h + hq) * p.seqlen_q_rounded + row];
   const bool dead = isinf(lse);
@@ -263,12 +300,13 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
     const int col = j0 + lane;
     float ds = 0.f;
     if (col < hi && !is_masked(m, row, col)) {
-      const float sc = (dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
-                       scale_log2;
+      float dfac;
+      const float sc = logit2(lc, dot_row(q_s[warp], kbase + (int64_t)col * p.k.row_stride, d) + mask_term<T>(p, bi, hq, row, col),
+                              row, col, &dfac);
       const float pij = exp2f(sc - lse2);
       float dp = dot_row(g_s[warp], vbase + (int64_t)col * p.v.row_stride, d);
       if (drop) dp = dropout_keep(dc, col) ? dp * rp : 0.f;   // dP = keep / p_keep * (dO . V)
-      ds = pij * (dp - dsum);
+      ds = pij * (dp - dsum) * dfac;
     }
     const int nj = min(32, hi - j0);
     for (int jj = 0; jj < nj; ++jj) {
@@ -309,7 +347,6 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
   const T *vrow = (const T *)p.v.ptr + elem_off(p.v, s_.k_boff, s_.k_row0 + col, hk);
   for (int e = lane; e < d; e += 32) { k_s[warp][e] = to_f(krow[e]); v_s[warp][e] = to_f(vrow[e]); }
   __syncwarp();
-  const float scale_log2 = p.softmax_scale * kLog2e;
   float dk[kMaxC], dv[kMaxC];
 #pragma unroll
   for (int c = 0; c < kMaxC; ++c) { dk[c] = 0.f; dv[c] = 0.f; }
@@ -317,6 +354,7 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
   const float rp = drop ? 1.f / (1.f - p.p_dropout) : 1.f;
   for (int hq = hq0; hq < hq1; ++hq) {
     const MaskCtx m = make_mask_ctx(p, bi, hq, s_.sq, s_.sk);
+    const LogitCtx lc = make_logit_ctx(p, bi, hq, s_.sk - s_.sq);
     int rlo = 0, rhi = s_.sq;
     if (m.causal) rlo = max(rlo, col - (m.bottom_right ? m.shift : 0));
     if (m.wr >= 0) rlo = max(rlo, col - m.shift - m.wr);
@@ -331,8 +369,9 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
       if (row < rhi && !is_masked(m, row, col)) {
         const float l = lse[row];
         if (!isinf(l)) {
-          const float sc = (dot_row(k_s[warp], qbase + (int64_t)row * p.q.row_stride, d) + mask_term<T>(p, bi, hq, row, col)) *
-                           scale_log2;
+          float dfac;
+          const float sc = logit2(lc, dot_row(k_s[warp], qbase + (int64_t)row * p.q.row_stride, d) + mask_term<T>(p, bi, hq, row, col),
+                                  row, col, &dfac);
           pij = exp2f(sc - l * kLog2e);
           float dp = dot_row(v_s[warp], gbase + (int64_t)row * p.dout.row_stride, d);
           float pd = pij;                                  // the weight dV sees: keep / p_keep * P
@@ -341,7 +380,7 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
             dp = keep ? dp * rp : 0.f;
             pd = keep ? pij * rp : 0.f;
           }
-          ds = pij * (dp - dsum[row]);
+          ds = pij * (dp - dsum[row]) * dfac;
           pij = pd;
         }
       }

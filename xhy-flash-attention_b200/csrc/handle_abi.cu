@@ -54,13 +54,13 @@ __global__ void lse_repack_kernel(float *packed, float *padded, const int *cu, i
 
 Params common_params(const Flash_fwd_params &h) {
   require(!h.is_e4m3 && !h.is_fp32, "only fp16 / bf16 inputs are supported");
-  require(h.softcap == 0.f, "softcap is not supported");
-  require(h.page_table == nullptr, "paged KV is not supported");
-  require(h.rotary_cos_ptr == nullptr && h.rotary_sin_ptr == nullptr, "rotary embedding is not supported");
+  require(h.softcap >= 0.f, "softcap must be >= 0");
   require(h.qv_ptr == nullptr, "qv is not supported");
-  require(h.kv_batch_idx == nullptr && h.leftpad_k == nullptr && h.seqused_q == nullptr,
-          "kv_batch_idx / leftpad_k / seqused_q are not supported");
-  require(h.knew_ptr == nullptr && h.vnew_ptr == nullptr, "knew / vnew: append with fa_b200_append_kv before the call");
+  require(h.seqused_q == nullptr, "seqused_q is not supported");
+  require(h.cu_seqlens_knew == nullptr, "cu_seqlens_knew is not supported");
+  require((h.knew_ptr == nullptr) == (h.vnew_ptr == nullptr), "knew_ptr and vnew_ptr go together");
+  require((h.rotary_cos_ptr == nullptr) == (h.rotary_sin_ptr == nullptr), "rotary_cos_ptr and rotary_sin_ptr go together");
+  require(h.rotary_cos_ptr == nullptr || h.knew_ptr != nullptr, "rotary embedding needs knew / vnew");
   require(h.p_dropout == 0.f || h.p_dropout >= 1.f, "dropout is not supported (p_dropout is the keep probability)");
   require(h.dv == 0 || h.dv == h.d, "dv != d is not supported");
   Params p;
@@ -83,6 +83,14 @@ Params common_params(const Flash_fwd_params &h) {
   p.causal_bottom_right = 1;                           // csrc/flashmask_v2/mask.h:85-97
   p.window_left = h.is_local ? h.window_size_left : -1;
   p.window_right = h.is_local ? h.window_size_right : -1;
+  p.softcap = h.softcap;
+  if (h.page_table) {                                  // csrc/flash_attn_v3/paged_kv.h: k/v are (num_pages, page_size, h_k, d)
+    require(h.page_size > 0 && h.num_pages > 0, "page_table needs page_size and num_pages");
+    p.page_table = h.page_table; p.page_table_batch_stride = h.page_table_batch_stride;
+    p.page_size = h.page_size; p.num_pages = h.num_pages;
+  }
+  p.kv_batch_idx = h.kv_batch_idx; p.b_k = h.b_k;
+  p.leftpad_k = h.leftpad_k;
   if (h.lt_start_ptr) {
     p.lt_start = h.lt_start_ptr; p.lt_end = h.lt_end_ptr; p.ut_start = h.ut_start_ptr; p.ut_end = h.ut_end_ptr;
     p.h_mask = h.h_flashmask > 0 ? h.h_flashmask : 1;
@@ -108,12 +116,80 @@ void set_split(Params &p, const Flash_fwd_params &h) {
   }
 }
 
+__global__ void add_lengths_kernel(int *out, const int *in, int add, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (in ? in[i] : 0) + add;
+}
+
+// knew / vnew (+ rotary): rotate q and k_new, append k_new / v_new at seqused_k, attend over seqused_k + seqlen_knew
+// (csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1090,1439,1542,1582).  Returns the stream-ordered scratch that
+// the caller frees after the attention launch.
+void *append_new_kv(Params &p, const Flash_fwd_params &h, cudaStream_t stream) {
+  require(h.seqlen_knew > 0, "seqlen_knew must be set with knew_ptr");
+  require(h.knew_batch_stride == h.vnew_batch_stride && h.knew_row_stride == h.vnew_row_stride &&
+          h.knew_head_stride == h.vnew_head_stride, "knew and vnew must share their strides");
+  const size_t esz = 2;
+  const size_t q_bytes = h.rotary_cos_ptr ? (size_t)h.b * h.seqlen_q * h.h * h.d * esz : 0;
+  const size_t k_bytes = h.rotary_cos_ptr ? (size_t)h.b * h.seqlen_knew * h.h_k * h.d * esz : 0;
+  auto up256 = [](size_t x) { return (x + 255) / 256 * 256; };
+  const size_t q_off = up256(sizeof(int) * (size_t)h.b), k_off = q_off + up256(q_bytes);   // [lengths | q_rot | k_rot]
+  char *scratch = nullptr;
+  FA_CUDA(cudaMallocAsync(&scratch, k_off + up256(k_bytes) + 256, stream));
+  int *lens_after = (int *)scratch;
+  const void *knew = h.knew_ptr;
+  int64_t nbs = h.knew_batch_stride, nrs = h.knew_row_stride, nhs = h.knew_head_stride;
+  try {
+    if (h.rotary_cos_ptr) {
+      require(h.rotary_dim > 0 && h.rotary_dim % 2 == 0 && h.rotary_dim <= h.d, "rotary_dim must be even and <= d");
+      void *q_rot = scratch + q_off, *k_rot = scratch + k_off;
+      const int64_t qh = h.d, qr = (int64_t)h.h * h.d, qb = qr * h.seqlen_q;
+      const int64_t kh = h.d, kr = (int64_t)h.h_k * h.d, kb = kr * h.seqlen_knew;
+      const int fixed = !(h.is_causal || h.is_local);
+      fa::rotary(h.q_ptr, q_rot, h.rotary_cos_ptr, h.rotary_sin_ptr, h.seqused_k, h.b, h.seqlen_q, h.h, h.d, h.rotary_dim,
+                 0x7fffffff, h.is_rotary_interleaved ? 1 : 0, fixed, p.is_bf16, h.q_batch_stride, h.q_row_stride,
+                 h.q_head_stride, qb, qr, qh, stream);
+      fa::rotary(h.knew_ptr, k_rot, h.rotary_cos_ptr, h.rotary_sin_ptr, h.seqused_k, h.b, h.seqlen_knew, h.h_k, h.d,
+                 h.rotary_dim, 0x7fffffff, h.is_rotary_interleaved ? 1 : 0, 0, p.is_bf16, h.knew_batch_stride,
+                 h.knew_row_stride, h.knew_head_stride, kb, kr, kh, stream);
+      p.q = tens(q_rot, qb, qr, qh);
+      knew = k_rot; nbs = kb; nrs = kr; nhs = kh;
+    }
+    p.seqused_k = h.seqused_k;                        // lengths before the append
+    // K and V may be rotated / plain: two single-tensor appends through the same entry
+    Params pk = p; pk.v = pk.k;
+    fa::append_kv_paged(pk, knew, knew, h.seqlen_knew, nbs, nrs, nhs, stream);
+    Params pv = p; pv.k = pv.v;
+    fa::append_kv_paged(pv, h.vnew_ptr, h.vnew_ptr, h.seqlen_knew, h.vnew_batch_stride, h.vnew_row_stride,
+                        h.vnew_head_stride, stream);
+    add_lengths_kernel<<<fa::ceil_div(h.b, 128), 128, 0, stream>>>(lens_after, h.seqused_k, h.seqlen_knew, h.b);
+    FA_CUDA(cudaGetLastError());
+    p.seqused_k = lens_after;
+  } catch (...) {
+    cudaFreeAsync(scratch, stream);
+    throw;
+  }
+  return scratch;
+}
+
 void run_fwd_handle(Flash_fwd_params *hp, cudaStream_t stream) {
   require(hp != nullptr, "null handle");
   const Flash_fwd_params &h = *hp;
   Params p = common_params(h);
   require(h.softmax_lse_ptr != nullptr, "softmax_lse_ptr must be set");
   set_split(p, h);
+  if (h.knew_ptr) {
+    require(h.cu_seqlens_q == nullptr && h.cu_seqlens_k == nullptr, "knew / vnew with cu_seqlens is not supported");
+    void *scratch = append_new_kv(p, h, stream);
+    p.softmax_lse = (float *)h.softmax_lse_ptr;
+    try {
+      if (h.num_splits > 1 || decode_shape(h)) fa::run_splitkv(p, stream); else fa::run_fwd(p, stream);
+    } catch (...) {
+      cudaFreeAsync(scratch, stream);
+      throw;
+    }
+    FA_CUDA(cudaFreeAsync(scratch, stream));
+    return;
+  }
   if (h.num_splits > 1 || decode_shape(h)) {
     p.softmax_lse = (float *)h.softmax_lse_ptr;
     fa::run_splitkv(p, stream);

@@ -477,53 +477,103 @@ def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None
     count (decode shapes: the wave model of ``fa_b200_decode_num_splits``; otherwise the reference heuristic,
     csrc/flashmask_v2/heuristics.h:22-59); partial results are merged by the
     LSE-combine kernel.  Inference only (no autograd).
+
+    Decode extras (csrc/flash_attn_v3/flash.h:96-140): ``block_table`` (paged cache, k/v_cache
+    (num_pages, page_size, nheads_k, headdim)), ``cache_batch_idx``, ``cache_leftpad`` (valid keys are
+    [leftpad, cache_seqlens)), ``rotary_cos/sin`` applied to ``k`` (and ``q``) before the append, ``softcap``,
+    ``alibi_slopes``.  The TMA decode kernel takes all of them when page_size % 64 == 0; other shapes use the
+    generic kernels.
     """
-    for name, val in (("rotary_cos", rotary_cos), ("rotary_sin", rotary_sin), ("cache_batch_idx", cache_batch_idx),
-                      ("cache_leftpad", cache_leftpad), ("block_table", block_table), ("alibi_slopes", alibi_slopes)):
-        if val is not None:
-            raise NotImplementedError(f"flash_attn_with_kvcache: {name} is not implemented (SURVEY.md 8(f) rank 4)")
-    if softcap != 0.0:
-        raise NotImplementedError("flash_attn_with_kvcache: softcap is not implemented (SURVEY.md 8(f) rank 4)")
     q, k_cache, v_cache = [_maybe_contiguous(x) for x in (q, k_cache, v_cache)]
     b, sq, h, d = q.shape
-    sk, h_k = k_cache.shape[1], k_cache.shape[2]
+    paged = block_table is not None
+    if paged:
+        if cache_batch_idx is not None:
+            raise ValueError("flash_attn_with_kvcache: block_table and cache_batch_idx are exclusive")
+        block_table = block_table.to(torch.int32).contiguous()
+        num_pages, page_size, h_k = k_cache.shape[0], k_cache.shape[1], k_cache.shape[2]
+        sk = block_table.shape[1] * page_size
+    else:
+        sk, h_k = k_cache.shape[1], k_cache.shape[2]
     if d % 8 != 0:
         raise RuntimeError("flash_attn_with_kvcache: head dimension must be a multiple of 8")
     if softmax_scale is None:
         softmax_scale = d ** (-0.5)
     lib = _capi.load()
     stream = _capi.stream_ptr(q.device)
+    is_bf16 = 1 if q.dtype == torch.bfloat16 else 0
     if cache_seqlens is not None and isinstance(cache_seqlens, int):
         cache_seqlens = torch.full((b,), cache_seqlens, dtype=torch.int32, device=q.device)
+    if cache_seqlens is not None:
+        cache_seqlens = cache_seqlens.to(torch.int32).contiguous()
+    keep = []   # tensors whose device pointers sit in `p` until the launches are enqueued
     with torch.cuda.device(q.device):
+        p = new_params(q.dtype)
+        p.k, p.v = tdesc(k_cache), tdesc(v_cache)
+        p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
+        p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+        if paged:
+            p.page_table, p.page_table_batch_stride = block_table.data_ptr(), block_table.stride(0)
+            p.page_size, p.num_pages = page_size, num_pages
+        if cache_batch_idx is not None:
+            cache_batch_idx = cache_batch_idx.to(torch.int32).contiguous()
+            p.kv_batch_idx, p.b_k = cache_batch_idx.data_ptr(), k_cache.shape[0]
+        if cache_leftpad is not None:
+            cache_leftpad = cache_leftpad.to(torch.int32).contiguous()
+            p.leftpad_k = cache_leftpad.data_ptr()
+        local = tuple(window_size) != (-1, -1)
+        if rotary_cos is not None:
+            # k_new is rotated at positions cache_seqlens + i; q at the same positions when causal / local, else every
+            # query row at cache_seqlens (csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1090,1582; rotary.h)
+            if k is None or rotary_sin is None:
+                raise ValueError("flash_attn_with_kvcache: rotary_cos / rotary_sin need k and v")
+            cos = rotary_cos.to(q.dtype).contiguous()
+            sin = rotary_sin.to(q.dtype).contiguous()
+            rdim = 2 * cos.shape[-1]
+
+            def rot(x, fixed):
+                y = torch.empty_like(x)
+                _capi.check(lib.fa_b200_rotary(
+                    x.data_ptr(), y.data_ptr(), cos.data_ptr(), sin.data_ptr(), ptr(cache_seqlens), x.shape[0],
+                    x.shape[1], x.shape[2], d, rdim, cos.shape[0], 1 if rotary_interleaved else 0, 1 if fixed else 0,
+                    is_bf16, x.stride(0), x.stride(1), x.stride(2), y.stride(0), y.stride(1), y.stride(2), stream),
+                    "fa_b200_rotary")
+                return y
+            q = rot(q, not (causal or local))
+            k = rot(_maybe_contiguous(k), False)
         seqused = cache_seqlens
         if k is not None:
             assert v is not None
             k, v = _maybe_contiguous(k), _maybe_contiguous(v)
+            if v.stride() != k.stride():
+                v = v.contiguous(); k = k.contiguous()
             s_new = k.shape[1]
-            is_bf16 = 1 if q.dtype == torch.bfloat16 else 0
-            for new, cache in ((k, k_cache), (v, v_cache)):  # K and V may have different strides: one call each
-                _capi.check(lib.fa_b200_append_kv(
-                    new.data_ptr(), new.data_ptr(), cache.data_ptr(), cache.data_ptr(), ptr(cache_seqlens),
-                    b, s_new, sk, h_k, d, is_bf16, new.stride(0), new.stride(1), new.stride(2),
-                    cache.stride(0), cache.stride(1), cache.stride(2), stream), "fa_b200_append_kv")
+            p.seqused_k = ptr(cache_seqlens)        # lengths before the append
+            _capi.check(lib.fa_b200_append_kv_paged(p, k.data_ptr(), v.data_ptr(), s_new, k.stride(0), k.stride(1),
+                                                    k.stride(2), stream), "fa_b200_append_kv_paged")
             seqused = (cache_seqlens + s_new) if cache_seqlens is not None else \
                 torch.full((b,), s_new, dtype=torch.int32, device=q.device)
-        p = new_params(q.dtype)
         out = torch.empty_like(q)
         lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
-        p.q, p.k, p.v, p.o = tdesc(q), tdesc(k_cache), tdesc(v_cache), tdesc(out)
+        p.q, p.o = tdesc(q), tdesc(out)
         p.softmax_lse = lse.data_ptr()
-        p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
-        p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
         p.softmax_scale = softmax_scale
         p.is_causal = 1 if causal else 0
         p.causal_bottom_right = 1
         p.window_left, p.window_right = window_size
         p.lse_empty_is_neg_inf = 1
+        p.softcap = float(softcap)
+        if alibi_slopes is not None:
+            alibi_slopes = alibi_slopes.to(device=q.device, dtype=torch.float32).contiguous()
+            if alibi_slopes.shape not in ((h,), (b, h)):
+                raise ValueError("flash_attn_with_kvcache: alibi_slopes must be (nheads,) or (batch, nheads)")
+            p.alibi_slopes = alibi_slopes.data_ptr()
+            p.alibi_batch_stride = h if alibi_slopes.dim() == 2 else 0
+        p.seqused_k = None
         if seqused is not None:
             seqused = seqused.to(torch.int32).contiguous()
             p.seqused_k = seqused.data_ptr()
+        keep += [block_table, cache_batch_idx, cache_leftpad, alibi_slopes, seqused, q]
         if num_splits <= 0:
             num_sm = torch.cuda.get_device_properties(q.device).multi_processor_count
             if sq * (h // h_k) <= 16 and d in (64, 128):   # the TMA-fed decode kernel (csrc/decode.cu)

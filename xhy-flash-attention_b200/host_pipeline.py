@@ -5,7 +5,8 @@ the results must end there -- the way ``bench.py`` measures its ``e2e`` number -
 way for BASELINE config 3) cost three times as long as the kernels if they are done one after the other.
 :class:`HostPipeline` cuts the batch into chunks and runs three streams: chunk *i+1* is copied host->device while
 chunk *i* runs forward + backward and the results of chunk *i-1* are copied device->host (PCIe is full duplex and the
-two directions use separate copy engines).  The batch dimension is independent for attention, so
+two directions use separate copy engines).  Inside a chunk the order is finer still: q/k/v travel before dout so the
+forward starts while dout is on the wire, and ``out`` leaves for the host while the backward is running.  The batch dimension is independent for attention, so
 chunking changes nothing in the results.  The kernels are the same ``fa_b200_fwd`` / ``fa_b200_bwd``; only the
 orchestration differs.
 """
@@ -62,28 +63,39 @@ class HostPipeline:
             hi = min(lo + c, b)
             n = hi - lo
             B = self._bufs[i % 2]
+            # host->device: q, k, v first (all the forward needs), dout behind them
             with torch.cuda.stream(self.s_in):
                 if self._in_free[i % 2] is not None:
                     self.s_in.wait_event(self._in_free[i % 2])
-                for name, src in (("q", q), ("k", k), ("v", v), ("do", dout)):
+                for name, src in (("k", k), ("v", v), ("q", q)):
                     B[name][:n].copy_(src[lo:hi], non_blocking=True)
-                ready = torch.cuda.Event()
-                ready.record(self.s_in)
+                qkv_ready = torch.cuda.Event()
+                qkv_ready.record(self.s_in)
+                B["do"][:n].copy_(dout[lo:hi], non_blocking=True)
+                do_ready = torch.cuda.Event()
+                do_ready.record(self.s_in)
+            # compute: the forward starts while dout is still on the wire
             with torch.cuda.stream(self.s_run):
-                self.s_run.wait_event(ready)
+                self.s_run.wait_event(qkv_ready)
                 if self._out_free[i % 2] is not None:
                     self.s_run.wait_event(self._out_free[i % 2])
                 o, qp, kp, vp, op, lse, _, _ = _flash_attn_forward(B["q"][:n], B["k"][:n], B["v"][:n], 0.0, scale,
                                                                    self.causal, False, _NO_MASK)
+                B["out"] = o
+                fwd_done = torch.cuda.Event()
+                fwd_done.record(self.s_run)
+                self.s_run.wait_event(do_ready)
                 _flash_attn_backward(B["do"][:n], qp, kp, vp, op, lse, B["dq"][:n], B["dk"][:n], B["dv"][:n], 0.0, scale,
                                      self.causal, mask=_NO_MASK)
-                B["out"] = o
                 done = torch.cuda.Event()
                 done.record(self.s_run)
                 self._in_free[i % 2] = done
+            # device->host: out leaves while the backward runs, the gradients after it
             with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(fwd_done)
+                out[lo:hi].copy_(B["out"][:n], non_blocking=True)
                 self.s_out.wait_event(done)
-                for name, dst in (("out", out), ("dq", dq), ("dk", dk), ("dv", dv)):
+                for name, dst in (("dq", dq), ("dk", dk), ("dv", dv)):
                     dst[lo:hi].copy_(B[name][:n], non_blocking=True)
                 B["out"].record_stream(self.s_out)
                 freed = torch.cuda.Event()
