@@ -52,6 +52,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// wait for a role that has nothing urgent to do (tile scheduler): sleeps between polls so that it does not take issue
+// slots from the warps that share its SM sub-partition
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(500);
+    if ((++spins & 0x3ff) == 0 && clock64() - t0 > 8000000000ll) __trap();
+  }
+}
+
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {

@@ -47,7 +47,9 @@ template <int HD> struct FwdSmem {
   static constexpr int kFmRecOff = (kTmemSlotOff + 16 + 31) / 32 * 32;
   static constexpr int kFmBarOff = kFmRecOff + 16 * 32;
   static constexpr int kFmVecOff = kFmBarOff + 2 * 16 * 8;
-  static constexpr int kTotal = kFmVecOff + 2 * 4 * kBN * 4;
+  // dynamic tile scheduler: ring of tile indices + full/empty barriers
+  static constexpr int kSchedOff = kFmVecOff + 2 * 4 * kBN * 4;
+  static constexpr int kTotal = kSchedOff + 4 * 4 + 2 * 4 * 8;   // room for up to 4 entries
   static constexpr int kDynBytes = kTotal + 1024;               // slack for manual 1024-byte alignment
 };
 
@@ -297,9 +299,48 @@ __device__ __forceinline__ void exp2_poly2(uint64_t x2, float &p0, float &p1) {
   p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(j1) << 23));
 }
 
+// Tile walk of one CTA.  Two policies:
+//   static  (dense, varlen): tile = blockIdx.x + i * gridDim.x.  Dense causal tiles of one head repeat with a period that
+//           the stride steps through evenly, so the static walk is balanced and costs nothing (measured: any ring in
+//           front of the roles costs ~3 % on BASELINE config 3).
+//   dynamic (FlashMask): the reference's DynamicPersistentTileScheduler (csrc/flashmask_v2/tile_scheduler.hpp:618-765,
+//           next tile by atomicAdd on a global counter).  With a column-sparse mask the work of a tile depends on the
+//           documents it touches, and a static stride left SMs idle (document mask over 256k tokens: 18.5 -> 13.7 ms).
+//           Warp 11 claims tiles -- the first is blockIdx.x, then gridDim.x + atomicAdd(counter) -- skips empty slots
+//           and publishes the indices through a 4-entry shared-memory ring that every other role reads.  It claims
+//           eagerly (one tile in hand beyond the ring): FlashMask tiles can be a few microseconds long, and a claim
+//           made only when a slot frees (tried: 2 entries, lazy) put the atomic's latency back on the producer's
+//           path (16.0 ms instead of 13.6).  -1 ends the stream.
+constexpr int kTileRing = 4;
+template <bool kDyn> struct TileWalk {
+  uint32_t val, full, empty, it;
+  int lane, cur, num_tiles;
+  __device__ __forceinline__ void setup(uint32_t base, int lane_, int num_tiles_) {
+    val = base; full = base + kTileRing * 4; empty = full + kTileRing * 8; it = 0; lane = lane_;
+    cur = blockIdx.x; num_tiles = num_tiles_;
+  }
+  __device__ __forceinline__ int next() {
+    if constexpr (!kDyn) {
+      const int t = cur;
+      cur += gridDim.x;
+      return t < num_tiles ? t : -1;
+    } else {
+      const uint32_t slot = it % kTileRing;
+      mbar_wait(full + slot * 8, (it / kTileRing) & 1);
+      int tile;
+      asm volatile("ld.shared.s32 %0, [%1];" : "=r"(tile) : "r"(val + slot * 4));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + slot * 8);
+      ++it;
+      return tile;
+    }
+  }
+};
+
 template <int HD, bool kBf16, bool kFM>
 __global__ void __launch_bounds__(kThreads, 1)
-fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles) {
+fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles,
+           int *__restrict__ tile_counter) {
   using L = FwdSmem<HD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -332,6 +373,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         mbar_init(sbase + L::kFmBarOff + (kFmRing + r) * 8, kFmConsumers);
       }
     }
+    if constexpr (kFM) {
+      for (int r = 0; r < kTileRing; ++r) {
+        mbar_init(sbase + L::kSchedOff + kTileRing * 4 + r * 8, 1);
+        mbar_init(sbase + L::kSchedOff + kTileRing * 4 + (kTileRing + r) * 8, 11);   // consumer warps 0-10
+      }
+    }
     fence_mbar_init();
   }
   if (warp == 8) tmem_alloc<512>(smem_u32(tmem_slot));
@@ -359,7 +406,9 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       uint32_t kv_it = 0, qcnt[2] = {0, 0};
       BlockSeq<kFM> seq;
       seq.setup(fm_ring, lane);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileWalk<kFM> tw;
+      tw.setup(sbase + L::kSchedOff, lane, num_tiles);
+      for (int tile = tw.next(); tile >= 0; tile = tw.next()) {
         TileInfo ti;
         if (!decode_tile(p, tile, num_m, ti)) continue;
         seq.init(p, ti);
@@ -367,17 +416,8 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         Blk blk;
         while (seq.next(blk)) {
           if (lane == 0) {
-#pragma unroll
-            for (int t = 0; t < 2; ++t) {
-              if (!blk.a[t] || q_loaded[t]) continue;
-              mbar_wait(bar(B_QEMPTY + t), (qcnt[t] & 1) ^ 1);
-              mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
-#pragma unroll
-              for (int hf = 0; hf < kHalves; ++hf)
-                tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + hf * kHalfBytes, &tm.q, bar(B_QFULL + t), hf * 64, ti.hq,
-                            ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
-              ++qcnt[t];
-            }
+            // K/V first: at a tile boundary the Q buffers are still owned by the previous tile's epilogue, the K/V ring
+            // is not -- the first key block of the next tile is on its way while that epilogue runs
 #pragma unroll
             for (int kv = 0; kv < 2; ++kv) {
               const uint32_t st = kv_it % kStages, ph = (kv_it / kStages) & 1;
@@ -388,6 +428,17 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
                 tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + hf * kHalfBytes, kv == 0 ? &tm.k : &tm.v,
                             bar(B_KVFULL + st), hf * 64, ti.hk, ti.k_row0 + blk.j * kBN, ti.k_b);
               ++kv_it;
+            }
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              if (!blk.a[t] || q_loaded[t]) continue;
+              mbar_wait(bar(B_QEMPTY + t), (qcnt[t] & 1) ^ 1);
+              mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
+#pragma unroll
+              for (int hf = 0; hf < kHalves; ++hf)
+                tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + hf * kHalfBytes, &tm.q, bar(B_QFULL + t), hf * 64, ti.hq,
+                            ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
+              ++qcnt[t];
             }
           }
 #pragma unroll
@@ -441,7 +492,9 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       };
       BlockSeq<kFM> seq;
       seq.setup(fm_ring, lane);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileWalk<kFM> tw;
+      tw.setup(sbase + L::kSchedOff, lane, num_tiles);
+      for (int tile = tw.next(); tile >= 0; tile = tw.next()) {
         TileInfo ti;
         if (!bcast0(decode_tile(p, tile, num_m, ti) ? 1 : 0)) continue;
         uniformize(ti);
@@ -509,10 +562,40 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     // ======================= FlashMask scanner =======================
     if constexpr (kFM) {
       uint32_t rec_it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      TileWalk<kFM> tw;
+      tw.setup(sbase + L::kSchedOff, lane, num_tiles);
+      for (int tile = tw.next(); tile >= 0; tile = tw.next()) {
         TileInfo ti;
         if (!decode_tile(p, tile, num_m, ti)) continue;
         fm_scan_tile(p, ti, fm_ring, rec_it, lane);
+      }
+    }
+   } else if (warp == 11) {
+    // ======================= tile scheduler (FlashMask only) =======================
+    if constexpr (kFM) {
+      const uint32_t val = sbase + L::kSchedOff, full = val + kTileRing * 4, empty = full + kTileRing * 8;
+      auto claim = [&]() {
+        int t = 0;
+        if (lane == 0) t = (int)gridDim.x + atomicAdd(tile_counter, 1);
+        return bcast0(t);
+      };
+      int tile = blockIdx.x;
+      for (uint32_t it = 0;; ++it) {
+        while (tile < num_tiles) {             // skip slots that hold no rows (m0 beyond the sequence)
+          TileInfo ti;
+          if (bcast0(decode_tile(p, tile, num_m, ti) ? 1 : 0)) break;
+          tile = claim();
+        }
+        const int pub = tile < num_tiles ? tile : -1;
+        const uint32_t slot = it % kTileRing;
+        mbar_wait_relaxed(empty + slot * 8, ((it / kTileRing) & 1) ^ 1);
+        if (lane == 0) {
+          asm volatile("st.shared.s32 [%0], %1;" ::"r"(val + slot * 4), "r"(pub) : "memory");
+          mbar_arrive(full + slot * 8);
+        }
+        __syncwarp();
+        if (pub < 0) break;
+        tile = claim();
       }
     }
    }
@@ -529,7 +612,9 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     BlockSeq<kFM> seq;
     seq.setup(fm_ring, lane);
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    TileWalk<kFM> tw;
+    tw.setup(sbase + L::kSchedOff, lane, num_tiles);
+    for (int tile = tw.next(); tile >= 0; tile = tw.next()) {
       TileInfo ti;
       if (!decode_tile(p, tile, num_m, ti)) continue;
       if (!ti.active[t]) {
@@ -812,10 +897,17 @@ template <int HD, bool kBf16, bool kFM> void launch_fwd(const Params &p, cudaStr
     attr_set = true;
   }
   const int grid = std::min(num_tiles, device_sm_count());
+  int *counter = nullptr;                          // stream-ordered scratch: the dynamic scheduler's tile counter
+  if (kFM) {
+    FA_CUDA(cudaMallocAsync(&counter, sizeof(int), s));
+    FA_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
+  }
   profile_mark(0, true, s);
-  kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles);
+  kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles, counter);
   profile_mark(0, false, s);
-  FA_CUDA(cudaGetLastError());
+  const cudaError_t launch_err = cudaGetLastError();
+  if (counter) FA_CUDA(cudaFreeAsync(counter, s));
+  FA_CUDA(launch_err);
   note_launch(2);
 }
 
