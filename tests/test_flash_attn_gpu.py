@@ -156,3 +156,32 @@ def test_host_pipeline_matches_device_path(fa, causal):
     torch.testing.assert_close(outs[1].float(), dq.cpu().float(), atol=2e-2, rtol=2e-2)   # dQ: fp32 atomics order
     with pytest.raises(ValueError):
         pipe.run(q.cuda(), k, v, g, *outs)
+
+
+def test_training_step_in_cuda_graph(fa):
+    """Forward + backward captured into a CUDA graph and replayed on new data in the same static buffers."""
+    torch.manual_seed(0)
+    b, s, h, hk, d = 2, 512, 8, 2, 128
+    q = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        torch.autograd.grad(fa.flash_attn_func(q, k, v, causal=True), (q, k, v), g)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = fa.flash_attn_func(q, k, v, causal=True)
+        dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    for _ in range(2):
+        with torch.no_grad():
+            for t in (q, k, v, g):
+                t.copy_(torch.randn_like(t))
+        graph.replay()
+        ref = oracle_all(q.detach(), k.detach(), v.detach(), g, orc.causal_mask_top_left(s, s).to(DEV))
+        check_2x("out", out, *ref["out"])
+        check_2x("dq", dq, *ref["dq"])
+        check_2x("dk", dk, *ref["dk"])
+        check_2x("dv", dv, *ref["dv"])

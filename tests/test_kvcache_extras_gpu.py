@@ -194,3 +194,38 @@ def test_softcap_alibi(fa, capi, sq, kind, softcap, alibi):
     check_lse(lse, lse_ref, atol=2e-2 if softcap > 0 else 2e-3)
     out3, lse3 = fa.flash_attn_with_kvcache(q, kc, vc, num_splits=3, return_softmax_lse=True, **kw)
     check_2x("out(split)", out3, ref, pt, atol=3e-3 if softcap > 0 else 1e-4)
+
+
+def test_decode_step_in_cuda_graph(fa):
+    """A decode step (append + split-KV attention + combine) captured ONCE into a CUDA graph and replayed: all state
+    that changes between steps (cache_seqlens, the new token's q/k/v) lives in static device buffers, the library
+    makes no host-side decision that depends on them, and its only allocation is stream-ordered."""
+    torch.manual_seed(8)
+    b, sk, h, hk, d = 4, 1024, 16, 4, 128
+    dt = torch.bfloat16
+    kc = torch.randn(b, sk, hk, d, device=DEV, dtype=dt)
+    vc = torch.randn_like(kc)
+    kc_ref, vc_ref = kc.clone(), vc.clone()
+    lens = torch.tensor([100, 1, 640, 1000], device=DEV, dtype=torch.int32)
+    lens_ref = lens.clone()
+    q_s = torch.zeros(b, 1, h, d, device=DEV, dtype=dt)
+    kn_s, vn_s = torch.zeros(b, 1, hk, d, device=DEV, dtype=dt), torch.zeros(b, 1, hk, d, device=DEV, dtype=dt)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):   # warm-up outside the capture (library load, attribute setting)
+        fa.flash_attn_with_kvcache(q_s, kc.clone(), vc.clone(), k=kn_s, v=vn_s, cache_seqlens=lens.clone(), causal=True,
+                                   num_splits=4)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out_s = fa.flash_attn_with_kvcache(q_s, kc, vc, k=kn_s, v=vn_s, cache_seqlens=lens, causal=True, num_splits=4)
+        lens.add_(1)
+    for step in range(3):
+        qn, kn, vn = torch.randn_like(q_s), torch.randn_like(kn_s), torch.randn_like(vn_s)
+        q_s.copy_(qn); kn_s.copy_(kn); vn_s.copy_(vn)
+        graph.replay()
+        ref, _, kc_ref, vc_ref = orc.kvcache_ref(qn, kc_ref, vc_ref, k=kn, v=vn, cache_seqlens=lens_ref, causal=True)
+        pt, _, _, _ = orc.kvcache_ref(qn, kc_ref, vc_ref, cache_seqlens=lens_ref + 1, causal=True, upcast=False)
+        lens_ref = lens_ref + 1
+        check_2x(f"out[step {step}]", out_s, ref, pt)
+    assert torch.equal(lens, lens_ref) and torch.equal(kc, kc_ref) and torch.equal(vc, vc_ref)

@@ -12,8 +12,8 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.jso
 python bench.py --steps 2 --warmup 3 > gpurun_out/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 > gpurun_out/ncu_launches.log 2>&1
-python tools/ncu_case.py 2 8192 32 8 1 2 > gpurun_out/plain_case.log 2>&1 &&
+python tools/ncu_case.py 8 8192 32 8 1 2 > gpurun_out/plain_case.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'fwd_kernel|bwd_kernel' -s 2 -c 2 -o gpurun_out/prof_r1 \
-    python tools/ncu_case.py 2 8192 32 8 1 2 > gpurun_out/ncu_full.log 2>&1
+    python tools/ncu_case.py 8 8192 32 8 1 2 > gpurun_out/ncu_full.log 2>&1
 tail -3 gpurun_out/pytest.log; tail -2 gpurun_out/smoke.log; for w in c3 c2 c4 c5b; do python -c "
 import json; d=json.load(open('gpurun_out/bench_$w.json')); print('$w', round(d['value'],1), d['unit'], round(d['ms_per_step'],3), 'ms', d.get('e2e',{}).get('value'), d.get('roofline',{}).get('frac'), d.get('encodings'))"; done
