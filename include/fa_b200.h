@@ -44,7 +44,7 @@ typedef struct fa_b200_params {
   float *softmax_lse;             /* (b, h, seqlen_q) fp32; varlen: (b, h, max_seqlen_q) */
   float *softmax_d;               /* bwd workspace (b, h, seqlen_q_rounded) fp32 */
   float *dq_accum;                /* bwd workspace (b, h, seqlen_q_rounded, d_rounded) fp32 */
-  float *dkv_accum;               /* bwd GQA workspace, 2 x (b, h_k, seqlen_k_rounded, d_rounded) fp32, or NULL */
+  float *dkv_accum;               /* reserved (the reference's GQA dk/dv fp32 workspace): unused, GQA groups are reduced in TMEM */
 
   /* ---- sizes ---- */
   int32_t b, seqlen_q, seqlen_k;  /* varlen: max_seqlen_q / max_seqlen_k */

@@ -1,6 +1,7 @@
 """GPU parity tests of the operator API against the oracle (mirrors the reference's tests/test_flash_attn.py:
 seeded randn inputs, mha/mqa/gqa, odd/unequal sequence lengths, head dims incl. non-multiples of 8, fp16/bf16,
 causal, packed variants, varlen via padding masks; outputs, LSE and gradients under the 2x rule)."""
+import importlib
 import math
 
 import pytest
@@ -185,3 +186,46 @@ def test_training_step_in_cuda_graph(fa):
         check_2x("dq", dq, *ref["dq"])
         check_2x("dk", dk, *ref["dk"])
         check_2x("dv", dv, *ref["dv"])
+
+
+@pytest.mark.parametrize("case", ["causal_gqa", "full", "window", "varlen"])
+def test_backward_deterministic(fa, case):
+    """``deterministic`` (flat C ABI: num_splits == 1, csrc/flash_attn/src/flash_bwd_kernel.h:3203-3208; v3 handle:
+    dq_semaphore): the fp32 adds into every dQ tile happen in key-block order, so repeated runs give the same BITS for
+    dq as well (dk / dv always do); the values agree with the default, unordered accumulation."""
+    itf = importlib.import_module("xhy-flash-attention_b200.flash_attn_interface")
+    torch.manual_seed(0)
+    b, s, h, hk, d = 3, 1000, 8, 2, 128
+    kw = {}
+    mask = itf._NO_MASK
+    causal = case in ("causal_gqa", "varlen")
+    if case == "varlen":
+        lens = [300, 1000, 77]
+        cu = torch.tensor([0, 300, 1300, 1377], device=DEV, dtype=torch.int32)
+        shape_q, shape_k = (sum(lens), h, d), (sum(lens), hk, d)
+        kw = dict(cu_seqlens_q=cu, cu_seqlens_k=cu, max_seqlen_q=max(lens), max_seqlen_k=max(lens))
+    else:
+        shape_q, shape_k = (b, s, h, d), (b, s, hk, d)
+    if case == "window":
+        mask = itf._Mask(window=(200, 50))
+    q = torch.randn(shape_q, device=DEV, dtype=torch.bfloat16)
+    k = torch.randn(shape_k, device=DEV, dtype=torch.bfloat16)
+    v = torch.randn(shape_k, device=DEV, dtype=torch.bfloat16)
+    g = torch.randn(shape_q, device=DEV, dtype=torch.bfloat16)
+    scale = d ** -0.5
+    out, qp, kp, vp, op, lse, _, _ = itf._flash_attn_forward(q, k, v, 0.0, scale, causal, False, mask,
+                                                              *([kw[n] for n in ("cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k")] if kw else []))
+
+    def bwd(det):
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        itf._flash_attn_backward(g, qp, kp, vp, op, lse, dq, dk, dv, 0.0, scale, causal, mask=mask, deterministic=det, **kw)
+        return dq, dk, dv
+
+    ref = bwd(False)
+    runs = [bwd(True) for _ in range(4)]
+    for r in runs[1:]:
+        for a, b_ in zip(runs[0], r):
+            assert torch.equal(a, b_), "deterministic backward changed bits between runs"
+    for a, b_ in zip(runs[0], ref):
+        torch.testing.assert_close(a.float(), b_.float(), atol=2e-2, rtol=2e-2)
+    assert torch.equal(runs[0][1], ref[1]) and torch.equal(runs[0][2], ref[2])   # dk, dv never depended on the order

@@ -118,6 +118,38 @@ __device__ __forceinline__ int64_t acc_tile_index(const Params &p, const BwdTile
   return (int64_t)t.acc_tile0 + (int64_t)hq * t.acc_tiles_per_head + m;
 }
 
+// Deterministic mode (fa_b200_params.deterministic; the flat C ABI's num_splits == 1, csrc/flash_attn/src/
+// flash_bwd_kernel.h:3203-3208; the v3 handle's dq_semaphore, mainloop_bwd_sm90_tma_gmma_ws.hpp:751-890): the fp32 adds
+// into a dq_accum tile happen in key-block order.  One int per tile counts the key blocks that have added so far; the
+// CTA of key block j waits for the count to reach (j - first key block that contributes to this query block).
+// CTAs are dispatched in blockIdx.x order, so the CTA being waited for is always resident or finished.
+__device__ __forceinline__ bool key_block_touches(const Params &p, const BwdTile &t, int j, int m) {
+  const int shift = t.sk - t.sq, shiftc = p.causal_bottom_right ? shift : 0;
+  const int n0 = j * kB;
+  if (n0 >= t.sk) return false;
+  int rlo = 0, rhi = t.sq;
+  const int c_last = min(n0 + kB, t.sk) - 1;
+  if (p.is_causal) rlo = max(rlo, n0 - shiftc);
+  if (p.window_right >= 0) rlo = max(rlo, n0 - shift - p.window_right);
+  if (p.window_left >= 0) rhi = min(rhi, c_last - shift + p.window_left + 1);
+  const int m_lo = rlo / kB, m_hi = (max(rhi, 0) + kB - 1) / kB;
+  return m >= m_lo && m < m_hi;
+}
+__device__ __forceinline__ int first_key_block(const Params &p, const BwdTile &t, int m) {
+  if (p.window_left < 0) return 0;           // without a left window every key block up to the causal bound contributes
+  int j = blockIdx.x;
+  while (j > 0 && key_block_touches(p, t, j - 1, m)) --j;
+  return j;
+}
+__device__ __forceinline__ int ld_acquire(const int *ptr) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add1(int *ptr) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(ptr) : "memory");
+}
+
 // The (q-head, query block) pairs one CTA visits, in the order every role walks them.  Per q-head the query blocks
 // are [m_lo, m_hi) minus the blocks that FlashMask covers completely for ALL keys of this CTA's key block: rows
 // [lts_max, lte_min) and [uts_max, ute_min) (per-block min/max of the mask vectors, flashmask_scan_kernel) -- at most
@@ -191,9 +223,9 @@ template <bool kFM> struct MCursor {
   }
 };
 
-template <int HD, bool kBf16, bool kFM>
+template <int HD, bool kBf16, bool kFM, bool kDet>
 __global__ void __launch_bounds__(kBwdThreads, 1)
-bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) {
+bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, int *__restrict__ dq_sem) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -371,7 +403,8 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
     for (int it = 0; it < n_it; ++it) {
       cur.step(p, t, it);
       const int hq = cur.hq, m = cur.m;
-      float *gtile = p.dq_accum + acc_tile_index(p, t, hq, m) * (int64_t)(p.d_rounded / 32) * (kB * 32);
+      const int64_t tile_idx = acc_tile_index(p, t, hq, m);
+      float *gtile = p.dq_accum + tile_idx * (int64_t)(p.d_rounded / 32) * (kB * 32);
       mbar_wait(bar(BB_DQ_FULL), it & 1);
       tc_fence_after();
       uint32_t v[HD / 32][32];
@@ -394,11 +427,23 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm) 
           fence_proxy_async_smem();
           named_bar_sync(4, 128);
           if (tid == 0) {
+            if (kDet && c == 0) {                // deterministic: wait for this tile's turn
+              const int turn = (int)blockIdx.x - first_key_block(p, t, m);
+              const long long t0 = clock64();
+              while (ld_acquire(dq_sem + tile_idx) != turn) {
+                __nanosleep(200);
+                if (clock64() - t0 > 20000000000ll) __trap();
+              }
+            }
             bulk_reduce_add_f32(gtile + c * (kB * 32), smem_u32(buf), kB * 32 * 4);
             bulk_commit();
           }
           ++g;
         }
+      }
+      if (kDet && tid == 0) {                    // all of this key block's adds have landed: pass the tile on
+        bulk_wait<0>();
+        red_release_add1(dq_sem + tile_idx);
       }
     }
     if (tid == 0) bulk_wait<0>();
@@ -671,7 +716,7 @@ bool out_ok(const fa_b200_tensor &t) {
   return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
 }
 
-template <int HD, bool kBf16, bool kFM> void launch_bwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDet = false> void launch_bwd(const Params &p, cudaStream_t s) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
@@ -681,10 +726,12 @@ template <int HD, bool kBf16, bool kFM> void launch_bwd(const Params &p, cudaStr
   tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
   tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
   // 1. dPsum + zeroing of the fp32 dQ accumulator (one kernel)
+  int64_t acc_tiles = 0;
   {
     int64_t tiles;
     if (packed) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
     else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
+    acc_tiles = tiles;
     const int64_t acc_vec4 = tiles * (p.d_rounded / 32) * (kB * 32) / 4;
     dim3 grid(ceil_div(p.seqlen_q_rounded, 16), p.h, p.b);
 #ifdef FA_AB_MEMSET
@@ -697,17 +744,24 @@ template <int HD, bool kBf16, bool kFM> void launch_bwd(const Params &p, cudaStr
   // 3. main kernel
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
-    auto kern = bwd_kernel<HD, kBf16, kFM>;
+    auto kern = bwd_kernel<HD, kBf16, kFM, kDet>;
     static bool attr_set = false;
     if (!attr_set) {
       FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
       attr_set = true;
     }
     dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
+    int *dq_sem = nullptr;
+    if (kDet) {                                 // one turn counter per dq_accum tile, stream-ordered scratch
+      FA_CUDA(cudaMallocAsync(&dq_sem, sizeof(int) * (size_t)acc_tiles, s));
+      FA_CUDA(cudaMemsetAsync(dq_sem, 0, sizeof(int) * (size_t)acc_tiles, s));
+    }
     profile_mark(1, true, s);
-    kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm);
+    kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm, dq_sem);
     profile_mark(1, false, s);
-    FA_CUDA(cudaGetLastError());
+    const cudaError_t launch_err = cudaGetLastError();
+    if (dq_sem) FA_CUDA(cudaFreeAsync(dq_sem, s));
+    FA_CUDA(launch_err);
     note_launch(2);
   }
   // 4. dQ conversion
@@ -728,6 +782,7 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
   if (p.d_rounded != round_up(p.d, 32) || p.seqlen_q_rounded % kB != 0 || p.seqlen_q_rounded < p.seqlen_q)
     return no("rounded sizes are not the documented ones");
   if (p.seqused_k) return no("seqused_k");
+  if (p.deterministic && p.lt_start) return no("deterministic + FlashMask (key blocks skip query blocks irregularly)");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -741,6 +796,11 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
 
 void sm100_bwd(const Params &p, cudaStream_t s) {
   const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
+  if (p.deterministic && !fm) {   // ordered dQ accumulation: its own instantiation, the default kernels carry none of it
+    if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, true>(p, s); else launch_bwd<64, false, false, true>(p, s); }
+    else { if (p.is_bf16) launch_bwd<128, true, false, true>(p, s); else launch_bwd<128, false, false, true>(p, s); }
+    return;
+  }
   if (p.d <= 64) {
     if (p.is_bf16) { if (fm) launch_bwd<64, true, true>(p, s); else launch_bwd<64, true, false>(p, s); }
     else { if (fm) launch_bwd<64, false, true>(p, s); else launch_bwd<64, false, false>(p, s); }

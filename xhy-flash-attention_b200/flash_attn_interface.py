@@ -187,11 +187,7 @@ def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p,
     dq_accum = torch.empty(acc_rows * d_r, dtype=torch.float32, device=q.device)
     p.q, p.k, p.v, p.o, p.dout, p.dq, p.dk, p.dv = [tdesc(t, packed=varlen) for t in (q, k, v, out, dout, dq, dk, dv)]
     p.softmax_lse, p.softmax_d, p.dq_accum = softmax_lse.data_ptr(), softmax_d.data_ptr(), dq_accum.data_ptr()
-    if h != h_k:
-        rows_k = (p.total_k + 128 * b) if varlen else b * sk_r
-        dkv_accum = torch.empty(2 * h_k * rows_k * d_r, dtype=torch.float32, device=q.device)
-        keep.append(dkv_accum)
-        p.dkv_accum = dkv_accum.data_ptr()
+    # no dk/dv accumulator: the kernels reduce a GQA group inside one CTA (TMEM), p.dkv_accum stays NULL
     p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
     p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = sq_r, sk_r, d_r
     p.softmax_scale = softmax_scale
