@@ -255,3 +255,38 @@ def test_varlen_packed_variants(fa, d, causal):
         check_2x("dk", dqkv[sl, 1][None], *ref["dk"])
         check_2x("dv", dqkv[sl, 2][None], *ref["dv"])
         o += n
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("mha_type", ["mha", "gqa", "mqa"])
+def test_varlen_from_padded_batch(fa, mha_type, causal):
+    """The reference's own varlen recipe (tests/test_flash_attn.py:657-783): padded batch + random padding masks ->
+    ``unpad_input`` -> ``flash_attn_varlen_func`` -> ``pad_input``, compared with ``attention_ref`` on the padded batch
+    with the same masks (outputs and input gradients, the 2x rule)."""
+    bp = fa.bert_padding
+    torch.manual_seed(0)
+    b, s, h, d = 5, 239, 6, 64
+    hk = {"mha": 6, "gqa": 2, "mqa": 1}[mha_type]
+    q = torch.randn(b, s, h, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    k = torch.randn(b, s, hk, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    v = torch.randn(b, s, hk, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    g = torch.randn(b, s, h, d, device=DEV, dtype=torch.float16)
+    lens = torch.tensor([239, 1, 100, 128, 57], device=DEV)
+    pad = torch.arange(s, device=DEV).view(1, s) < lens.view(b, 1)     # one mask for q and k: causal stays well defined
+    qu, idx_q, cu_q, max_q = bp.unpad_input(q, pad)
+    ku, _, cu_k, max_k = bp.unpad_input(k, pad)
+    vu, _, _, _ = bp.unpad_input(v, pad)
+    out_u = fa.flash_attn_varlen_func(qu, ku, vu, cu_q, cu_k, max_q, max_k, 0.0, None, causal)
+    out = bp.pad_input(out_u, idx_q, b, s)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    qd, kd, vd = [t.detach().clone().requires_grad_(True) for t in (q, k, v)]
+    ref, _ = orc.attention_ref(qd, kd, vd, pad, pad, 0.0, None, causal=causal)
+    rq, rk, rv = torch.autograd.grad(ref, (qd, kd, vd), g)
+    qd2, kd2, vd2 = [t.detach().clone().requires_grad_(True) for t in (q, k, v)]
+    pt, _ = orc.attention_ref(qd2, kd2, vd2, pad, pad, 0.0, None, causal=causal, upcast=False, reorder_ops=True)
+    pq, pk, pv = torch.autograd.grad(pt, (qd2, kd2, vd2), g)
+    check_2x("out", out, ref, pt)
+    check_2x("dq", dq, rq, pq)
+    check_2x("dk", dk, rk, pk)
+    check_2x("dv", dv, rv, pv)
+    assert (out[~pad] == 0).all() and (dq[~pad] == 0).all() and (dk[~pad] == 0).all()

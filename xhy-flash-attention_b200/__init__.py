@@ -8,6 +8,7 @@ The directory name is not a Python identifier; import it with
 __version__ = "0.1.0"
 
 from .host_pipeline import HostPipeline  # noqa: F401
+from . import bert_padding  # noqa: F401
 from .flash_attn_interface import (  # noqa: F401
     flash_attn_func,
     flash_attn_kvpacked_func,
