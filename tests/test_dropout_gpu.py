@@ -86,3 +86,34 @@ def test_dropout_varlen_and_packed(fa):
         check_2x("out", out[a:e].unsqueeze(0), ref[0], pt[0])
         for j, name in enumerate(("dq", "dk", "dv")):
             check_2x(name, dqkv[a:e, j].unsqueeze(0), ref[2 + j], pt[2 + j])
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,sk,d,h,hk", [(256, 256, 128, 4, 4), (300, 515, 128, 6, 2), (128, 384, 64, 4, 1), (1000, 1000, 96, 2, 2)])
+def test_dropout_tcgen05_path(fa, capi, sq, sk, d, h, hk, causal, dtype):
+    """Dropout without return_attn_probs takes the tcgen05 kernels (kDrop instantiations).  The mask is a pure function
+    of (seed, offset, b, h, row, col), so the same seed through the generic kernels (which also emit S_dmask) gives the
+    same mask: the fast path is checked against the fp32 oracle fed with THAT mask, forward and backward."""
+    b, p = 2, 0.17
+    torch.manual_seed(1)
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=dtype, requires_grad=True)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=dtype)
+    torch.manual_seed(7)
+    out = fa.flash_attn_func(q, k, v, p, None, causal)
+    assert capi.last_kernel_kind() == 2, "dropout forward did not take the tcgen05 kernel"
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    kind_bwd = capi.last_kernel_kind()
+    torch.manual_seed(7)
+    out_g, _, S = fa.flash_attn_func(q, k, v, p, None, causal, True)      # generic kernels, same seed
+    keep = S[:, :, :sq, :sk].float() >= 0
+    ref = _ref_with_mask(q, k, v, g, keep, causal, p)
+    pt = _ref_with_mask(q, k, v, g, keep, causal, p, upcast=False, reorder_ops=True)
+    check_2x("out", out, ref[0], pt[0])
+    check_2x("dq", dq, ref[2], pt[2])
+    check_2x("dk", dk, ref[3], pt[3])
+    check_2x("dv", dv, ref[4], pt[4])
+    torch.testing.assert_close(out.float(), out_g.float(), atol=2e-2, rtol=2e-2)
+    assert kind_bwd in (1, 2)

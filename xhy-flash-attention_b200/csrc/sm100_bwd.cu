@@ -223,7 +223,7 @@ template <bool kFM> struct MCursor {
   }
 };
 
-template <int HD, bool kBf16, bool kFM, bool kDet>
+template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, int *__restrict__ dq_sem) {
   using L = BwdSmem<HD>;
@@ -459,6 +459,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
     const uint32_t ds_row_a = sbase + L::kDS + wg * kHalfBytes + r * 128;
     const int shift = t.sk - t.sq;
     const int shiftc = p.causal_bottom_right ? shift : 0;
+    const float rp_drop = kDrop ? 1.f / (1.f - p.p_dropout) : 1.f;
     MCursor<kFM> cur;
     cur.init(t);
     for (int it = 0; it < n_it; ++it) {
@@ -501,6 +502,33 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
             if (is_masked(mc, m0 + wg * 64 + i, col)) mbits[i >> 5] |= 1u << (i & 31);
         }
       }
+      // Dropout (kDrop): keep bits of this thread's 64 (query, key) pairs.  The mask is dropout_keep() of common.h: one
+      // Philox call covers 16 consecutive KEY columns of one query row, i.e. the 16 lanes of a half warp want one byte
+      // each of the same call.  Each lane therefore runs the generator for one row of a 16-row group and the half
+      // warp exchanges the results by shuffles (16 steps: at step s a lane serves the lane s places below it and is
+      // served by the lane s places above).  Done before the wait for S, under the MMA that is in flight.
+      uint32_t kb[2] = {0xffffffffu, 0xffffffffu};
+      if constexpr (kDrop) {
+        kb[0] = kb[1] = 0u;
+        const int l16 = lane & 15;
+        const uint32_t thr = (uint32_t)floorf((1.f - p.p_dropout) * 255.f);
+        const uint64_t ncg = (uint64_t)((p.seqlen_k + 15) / 16);
+        const uint64_t cg = (uint64_t)((t.n0 + (warp % 4) * 32 + (lane & 16)) >> 4);
+        const uint64_t head_base = ((uint64_t)t.bi * p.h + hq) * (uint64_t)p.seqlen_q;
+#pragma unroll
+        for (int ig = 0; ig < 4; ++ig) {
+          const uint64_t rrow = (uint64_t)(m0 + wg * 64 + ig * 16 + l16);
+          const uint4 rnd = philox4x32_10(p.philox_seed, (head_base + rrow) * ncg + cg, p.philox_offset);
+#pragma unroll
+          for (int s_ = 0; s_ < 16; ++s_) {
+            const int wi = ((l16 - s_) & 15) >> 2;         // word the lane I serve at this step wants
+            const uint32_t wsel = wi == 0 ? rnd.x : wi == 1 ? rnd.y : wi == 2 ? rnd.z : rnd.w;
+            const int src16 = (l16 + s_) & 15;             // row (inside the group) I am served with
+            const uint32_t got = __shfl_sync(0xffffffffu, wsel, (lane & 16) | src16);
+            if (((got >> ((l16 & 3) * 8)) & 0xffu) <= thr) kb[ig >> 1] |= 1u << ((ig & 1) * 16 + src16);
+          }
+        }
+      }
       mbar_wait(bar(BB_Q_FULL + st), (it >> 1) & 1);   // LSE / dPsum rows of this query block are in smem
       mbar_wait(bar(BB_S_FULL), it & 1);
       tc_fence_after();
@@ -525,8 +553,15 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
             if ((mb >> i) & 1u) pr[c2 * 32 + i] = 0.f;
         }
         uint32_t pk[16];
+        if constexpr (kDrop) {   // dV sees the dropped weights (1 / p_keep is applied to dV in the epilogue)
 #pragma unroll
-        for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[c2 * 32 + 2 * i], pr[c2 * 32 + 2 * i + 1]);
+          for (int i = 0; i < 16; ++i)
+            pk[i] = pack2<kBf16>(((kb[c2] >> (2 * i)) & 1u) ? pr[c2 * 32 + 2 * i] : 0.f,
+                                 ((kb[c2] >> (2 * i + 1)) & 1u) ? pr[c2 * 32 + 2 * i + 1] : 0.f);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[c2 * 32 + 2 * i], pr[c2 * 32 + 2 * i + 1]);
+        }
         tmem_st16(tP + c2 * 16, pk);
       }
       tmem_wait_st();
@@ -545,10 +580,18 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           const float4 d4 = lds128(dpsum_a + (c2 * 32 + i) * 4);
-          const float e0 = pr[c2 * 32 + i + 0] * (__uint_as_float(dp[i + 0]) - d4.x);
-          const float e1 = pr[c2 * 32 + i + 1] * (__uint_as_float(dp[i + 1]) - d4.y);
-          const float e2 = pr[c2 * 32 + i + 2] * (__uint_as_float(dp[i + 2]) - d4.z);
-          const float e3 = pr[c2 * 32 + i + 3] * (__uint_as_float(dp[i + 3]) - d4.w);
+          float g0 = __uint_as_float(dp[i + 0]), g1 = __uint_as_float(dp[i + 1]), g2 = __uint_as_float(dp[i + 2]),
+                g3 = __uint_as_float(dp[i + 3]);
+          if constexpr (kDrop) {   // dP = keep / p_keep * (dO . V)
+            g0 = ((kb[c2] >> (i + 0)) & 1u) ? g0 * rp_drop : 0.f;
+            g1 = ((kb[c2] >> (i + 1)) & 1u) ? g1 * rp_drop : 0.f;
+            g2 = ((kb[c2] >> (i + 2)) & 1u) ? g2 * rp_drop : 0.f;
+            g3 = ((kb[c2] >> (i + 3)) & 1u) ? g3 * rp_drop : 0.f;
+          }
+          const float e0 = pr[c2 * 32 + i + 0] * (g0 - d4.x);
+          const float e1 = pr[c2 * 32 + i + 1] * (g1 - d4.y);
+          const float e2 = pr[c2 * 32 + i + 2] * (g2 - d4.z);
+          const float e3 = pr[c2 * 32 + i + 3] * (g3 - d4.w);
           pk[i / 2] = pack2<kBf16>(e0, e1);
           pk[i / 2 + 1] = pack2<kBf16>(e2, e3);
         }
@@ -576,7 +619,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
       T *dst = which == 0 ? dv_row : dk_row;
-      const float mul = which == 0 ? 1.f : p.softmax_scale;
+      const float mul = which == 0 ? rp_drop : p.softmax_scale;
 #pragma unroll
       for (int c = 0; c < kColsPerWg / 32; ++c) {
         uint32_t v[32];
@@ -716,7 +759,7 @@ bool out_ok(const fa_b200_tensor &t) {
   return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
 }
 
-template <int HD, bool kBf16, bool kFM, bool kDet = false> void launch_bwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false> void launch_bwd(const Params &p, cudaStream_t s) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
@@ -744,7 +787,7 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false> void launch_bwd(const
   // 3. main kernel
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
-    auto kern = bwd_kernel<HD, kBf16, kFM, kDet>;
+    auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop>;
     static bool attr_set = false;
     if (!attr_set) {
       FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
@@ -783,6 +826,7 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
     return no("rounded sizes are not the documented ones");
   if (p.seqused_k) return no("seqused_k");
   if (p.deterministic && p.lt_start) return no("deterministic + FlashMask (key blocks skip query blocks irregularly)");
+  if (p.deterministic && p.p_dropout > 0.f) return no("deterministic + dropout");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -799,6 +843,16 @@ void sm100_bwd(const Params &p, cudaStream_t s) {
   if (p.deterministic && !fm) {   // ordered dQ accumulation: its own instantiation, the default kernels carry none of it
     if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, true>(p, s); else launch_bwd<64, false, false, true>(p, s); }
     else { if (p.is_bf16) launch_bwd<128, true, false, true>(p, s); else launch_bwd<128, false, false, true>(p, s); }
+    return;
+  }
+  if (p.p_dropout > 0.f) {        // dropout: its own instantiations as well
+    if (p.d <= 64) {
+      if (p.is_bf16) { if (fm) launch_bwd<64, true, true, false, true>(p, s); else launch_bwd<64, true, false, false, true>(p, s); }
+      else { if (fm) launch_bwd<64, false, true, false, true>(p, s); else launch_bwd<64, false, false, false, true>(p, s); }
+    } else {
+      if (p.is_bf16) { if (fm) launch_bwd<128, true, true, false, true>(p, s); else launch_bwd<128, true, false, false, true>(p, s); }
+      else { if (fm) launch_bwd<128, false, true, false, true>(p, s); else launch_bwd<128, false, false, false, true>(p, s); }
+    }
     return;
   }
   if (p.d <= 64) {

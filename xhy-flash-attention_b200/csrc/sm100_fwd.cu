@@ -337,7 +337,7 @@ template <bool kDyn> struct TileWalk {
   }
 };
 
-template <int HD, bool kBf16, bool kFM>
+template <int HD, bool kBf16, bool kFM, bool kDrop>
 __global__ void __launch_bounds__(kThreads, 1)
 fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles,
            int *__restrict__ tile_counter) {
@@ -626,6 +626,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         continue;
       }
       const int row = ti.m0 + t * kBM + r_in_tile;
+      // dropout (kDrop instantiation): the mask of common.h's dropout_keep -- one Philox-4x32-10 call per 16
+      // consecutive columns of a row, a weight is kept iff its byte <= floor(255 * p_keep).  A thread owns a row, so
+      // every 32-column chunk of P costs it two calls.  The row sum is taken BEFORE dropout and 1 / p_keep is folded
+      // into the final normalisation (flash_fwd_kernel.h:399-409, softmax.h:381-447).
+      DropCtx dctx;
+      if constexpr (kDrop) dctx = make_drop_ctx(p, ti.bi, ti.hq, row);
       T *optr = (T *)p.o.ptr + (int64_t)ti.q_b * p.o.batch_stride + (int64_t)(ti.q_row0) * p.o.row_stride +
                 (int64_t)ti.hq * p.o.head_stride;
       float *lse_ptr = p.softmax_lse + ((int64_t)ti.bi * p.h + ti.hq) * p.seqlen_q;
@@ -756,6 +762,8 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t pk[16];
+          uint4 rnd = make_uint4(0, 0, 0, 0);
+          (void)rnd;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
@@ -768,6 +776,14 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
               p0 = ex2(x0); p1 = ex2(x1);
             }
             if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
+            if constexpr (kDrop) {
+              if (i % 8 == 0)
+                rnd = philox4x32_10(dctx.seed, dctx.row_base + (uint32_t)((blk.j * kBN + c * 32 + 2 * i) >> 4), dctx.offset);
+              const int e = (2 * i) & 15;                       // position of the pair inside its 16-column group
+              const uint32_t w = e < 4 ? rnd.x : e < 8 ? rnd.y : e < 12 ? rnd.z : rnd.w;
+              if (((w >> ((e & 3) * 8)) & 0xffu) > dctx.threshold) p0 = 0.f;
+              if (((w >> (((e + 1) & 3) * 8)) & 0xffu) > dctx.threshold) p1 = 0.f;
+            }
             pk[i] = pack2<kBf16>(p0, p1);
           }
           tmem_st16(tS + c * 16, pk);
@@ -803,7 +819,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       // A row with at least one visible key has l >= ~1 (its maximum contributes 2^0).  Masked elements that went
       // through the polynomial exp2 contribute 2^-125 each instead of 0, so "no visible key" is l below a tiny bound.
       const bool nonempty = l > 1e-30f;
-      const float inv = nonempty ? 1.f / l : 0.f;
+      const float inv = nonempty ? (kDrop ? 1.f / ((1.f - p.p_dropout) * l) : 1.f / l) : 0.f;
       uint8_t *stage = smem + L::kQOff + t * L::kTileBytes;  // Q_t is dead: all S MMAs of this tile have completed
       constexpr int kChunks = HD / 8;                        // 16-byte chunks per row
 #pragma unroll
@@ -877,7 +893,7 @@ bool tma_ok(const fa_b200_tensor &t, int heads, int batch) {
   return true;
 }
 
-template <int HD, bool kBf16, bool kFM> void launch_fwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDrop> void launch_fwd(const Params &p, cudaStream_t s) {
   using L = FwdSmem<HD>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
@@ -890,7 +906,7 @@ template <int HD, bool kBf16, bool kFM> void launch_fwd(const Params &p, cudaStr
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
   if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
-  auto kern = fwd_kernel<HD, kBf16, kFM>;
+  auto kern = fwd_kernel<HD, kBf16, kFM, kDrop>;
   static bool attr_set = false;
   if (!attr_set) {
     FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
@@ -929,15 +945,20 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
   return true;
 }
 
-void sm100_fwd(const Params &p, cudaStream_t s) {
+namespace {
+
+template <int HD, bool kBf16> void dispatch_fwd(const Params &p, cudaStream_t s) {
   const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
-  if (p.d <= 64) {
-    if (p.is_bf16) { if (fm) launch_fwd<64, true, true>(p, s); else launch_fwd<64, true, false>(p, s); }
-    else { if (fm) launch_fwd<64, false, true>(p, s); else launch_fwd<64, false, false>(p, s); }
-  } else {
-    if (p.is_bf16) { if (fm) launch_fwd<128, true, true>(p, s); else launch_fwd<128, true, false>(p, s); }
-    else { if (fm) launch_fwd<128, false, true>(p, s); else launch_fwd<128, false, false>(p, s); }
-  }
+  const bool drop = p.p_dropout > 0.f;
+  if (fm) { if (drop) launch_fwd<HD, kBf16, true, true>(p, s); else launch_fwd<HD, kBf16, true, false>(p, s); }
+  else { if (drop) launch_fwd<HD, kBf16, false, true>(p, s); else launch_fwd<HD, kBf16, false, false>(p, s); }
+}
+
+}  // namespace
+
+void sm100_fwd(const Params &p, cudaStream_t s) {
+  if (p.d <= 64) { if (p.is_bf16) dispatch_fwd<64, true>(p, s); else dispatch_fwd<64, false>(p, s); }
+  else { if (p.is_bf16) dispatch_fwd<128, true>(p, s); else dispatch_fwd<128, false>(p, s); }
 }
 
 }  // namespace fa
