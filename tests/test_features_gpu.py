@@ -290,3 +290,65 @@ def test_varlen_from_padded_batch(fa, mha_type, causal):
     check_2x("dk", dk, rk, pk)
     check_2x("dv", dv, rv, pv)
     assert (out[~pad] == 0).all() and (dq[~pad] == 0).all() and (dk[~pad] == 0).all()
+
+
+def test_more_than_2g_elements(fa):
+    """Maximum sizes: q / out / dq with more than 2^31 elements (4.9 GB each in bf16), so every element offset in the
+    kernels has to be 64-bit.  Sliding-window attention keeps the arithmetic small; the far end of the tensors (offsets
+    beyond 2^31 elements and 2^32 bytes) is checked against the oracle on a slice that contains its whole window."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60 * 2 ** 30:
+        pytest.skip("needs ~45 GB of device memory")
+    torch.manual_seed(0)
+    b, s, h, hk, d, w = 1, 300032, 64, 2, 128, 128
+    assert b * s * h * d > 2 ** 31
+    q = torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16).requires_grad_(True)
+    k = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16).requires_grad_(True)
+    v = torch.randn(b, s, hk, d, device=DEV, dtype=torch.bfloat16).requires_grad_(True)
+    out = fa.flash_attn_func(q, k, v, causal=True, window_size=(w, 0))
+    g = torch.zeros_like(out)
+    lo, hi = s - 1024, s                      # the slice that is checked: the last 1024 rows / keys
+    g[:, lo:hi] = torch.randn(b, hi - lo, h, d, device=DEV, dtype=torch.bfloat16)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    torch.cuda.synchronize()
+    qs, ks, vs = [t.detach()[:, lo - w:hi].clone() for t in (q, k, v)]     # rows lo-w.. so that every window is complete
+    n = hi - lo + w
+    mask = orc.causal_mask_bottom_right(n, n) | orc.local_mask(n, n, w, 0)
+    ref = oracle_all(qs, ks, vs, g[:, lo - w:hi], mask.to(DEV))
+    sl = slice(w, n)                          # the rows / keys of the slice proper
+    check_2x("out", out[:, lo:hi], ref["out"][0][:, sl], ref["out"][1][:, sl])
+    check_2x("dq", dq[:, lo:hi], ref["dq"][0][:, sl], ref["dq"][1][:, sl])
+    check_2x("dk", dk[:, lo:hi], ref["dk"][0][:, sl], ref["dk"][1][:, sl])
+    check_2x("dv", dv[:, lo:hi], ref["dv"][0][:, sl], ref["dv"][1][:, sl])
+    assert (dq[:, : lo - w] == 0).all() and (dk[:, : lo - 2 * w] == 0).all()   # nothing leaks to the untouched front
+
+
+@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+def test_varlen_empty_sequences(fa, generic):
+    """Empty inputs: sequences of length 0 inside a packed batch (cu_seqlens with repeated offsets), on the query side,
+    the key side or both.  A query with no key gives out = 0 and no gradient; a key with no query gets dk = dv = 0."""
+    torch.manual_seed(0)
+    lens_q = [5, 0, 130, 0, 64]
+    lens_k = [7, 3, 0, 0, 64]
+    h, hk, d = 4, 2, 64
+    tq, tk = sum(lens_q), sum(lens_k)
+    q = torch.randn(tq, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(tk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(tk, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(tq, h, d, device=DEV, dtype=torch.bfloat16)
+    cu_q, cu_k = _lens_to_cu(lens_q), _lens_to_cu(lens_k)
+    out = fa.flash_attn_varlen_func(q, k, v, cu_q, cu_k, max(lens_q), max(lens_k), 0.0, None, False, _force_generic=generic)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), g)
+    assert not any(torch.isnan(t.float()).any() for t in (out, dq, dk, dv))
+    oq = ok = 0
+    for lq, lk in zip(lens_q, lens_k):
+        sq_, sk_ = slice(oq, oq + lq), slice(ok, ok + lk)
+        if lq and lk:
+            ref = oracle_all(q.detach()[sq_][None], k.detach()[sk_][None], v.detach()[sk_][None], g[sq_][None])
+            check_2x("out", out[sq_][None], *ref["out"])
+            check_2x("dq", dq[sq_][None], *ref["dq"])
+            check_2x("dk", dk[sk_][None], *ref["dk"])
+            check_2x("dv", dv[sk_][None], *ref["dv"])
+        else:
+            assert (out[sq_] == 0).all() and (dq[sq_] == 0).all() and (dk[sk_] == 0).all() and (dv[sk_] == 0).all()
+        oq += lq; ok += lk
