@@ -1,6 +1,6 @@
-"""Small invocations of every kernel family, for compute-sanitizer (memcheck / synccheck / racecheck):
-    compute-sanitizer --tool memcheck python tools/sanitize_case.py
-Shapes are tiny (the tools slow kernels down 10-100x) but hit: tcgen05 fwd/bwd (dense causal GQA, d64, ragged
+"""Small invocations of every kernel family, one after the other (a quick "does every path launch" run; also usable under a debugger or profiler):
+    python tools/all_kernels_case.py [train|flashmask|decode|generic]
+Shapes are tiny but hit: tcgen05 fwd/bwd (dense causal GQA, d64, ragged
 lengths, varlen, FlashMask with skipped + partial blocks), decode kernel (contiguous, paged, leftpad, splits + combine),
 generic kernels (d 256, dropout), rotary + append, LSE merge."""
 import importlib, os, sys
