@@ -16,10 +16,10 @@ torch.manual_seed(0)
 dev, dt = "cuda", torch.bfloat16
 
 
-def dense(b, s, causal=True, h=32, hk=8):
-    q = torch.randn(b, s, h, 128, device=dev, dtype=dt, requires_grad=True)
-    k = torch.randn(b, s, hk, 128, device=dev, dtype=dt, requires_grad=True)
-    v = torch.randn(b, s, hk, 128, device=dev, dtype=dt, requires_grad=True)
+def dense(b, s, causal=True, h=32, hk=8, d=128):
+    q = torch.randn(b, s, h, d, device=dev, dtype=dt, requires_grad=True)
+    k = torch.randn(b, s, hk, d, device=dev, dtype=dt, requires_grad=True)
+    v = torch.randn(b, s, hk, d, device=dev, dtype=dt, requires_grad=True)
     g = torch.randn_like(q)
     def step():
         o = fa.flash_attn_func(q, k, v, causal=causal)
@@ -56,7 +56,7 @@ def fmdoc(lens, h=32, hk=8):
 
 gen = torch.Generator().manual_seed(0)
 rag = [int(x) for x in (128 + torch.rand(32, generator=gen) * 7800).round().tolist()]
-cases = {"c3 b8 s8192": dense(8, 8192), "b64 s1024": dense(64, 1024), "b16 s4096": dense(16, 4096),
+cases = {"c3 b8 s8192": dense(8, 8192), "d64 b8 s8192 h32/8": dense(8, 8192, True, 32, 8, 64), "b64 s1024": dense(64, 1024), "b16 s4096": dense(16, 4096),
          "c2 b8 s2048 nc h16": dense(8, 2048, False, 16, 16), f"varlen 32 seqs {sum(rag)} tok": varlen(rag),
          f"fmdoc 32 docs {sum(rag)} tok": fmdoc(rag)}
 only = os.environ.get("AB_CASES")

@@ -1,5 +1,6 @@
 // common.h -- shared host/device definitions for libflashattn_b200.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -63,6 +64,17 @@ void flashmask_prepare(const Params &p, int block_n, cudaStream_t s, bool with_l
 void append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache, const int32_t *cache_seqlens,
                int batch, int seqlen_new, int seqlen_cache, int h_k, int d, int is_bf16,
                int64_t nbs, int64_t nrs, int64_t nhs, int64_t cbs, int64_t crs, int64_t chs, cudaStream_t s);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device setting: remember it per (kernel instantiation, device)
+// so that one process driving several GPUs (Paddle's usual mode) sets it on each of them.  `done` is the caller's
+// function-local static array, one flag per device ordinal.
+template <typename Kern> inline void ensure_dynamic_smem(Kern kern, int bytes, std::atomic<bool> (&done)[64]) {
+  int dev = 0;
+  FA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && done[dev].load(std::memory_order_acquire)) return;
+  FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  if (dev >= 0 && dev < 64) done[dev].store(true, std::memory_order_release);
+}
+
 void append_kv_paged(const Params &p, const void *k_new, const void *v_new, int seqlen_new, int64_t nbs, int64_t nrs,
                      int64_t nhs, cudaStream_t s);
 void rotary(const void *x, void *out, const void *cosp, const void *sinp, const int32_t *offsets, int batch, int seqlen,

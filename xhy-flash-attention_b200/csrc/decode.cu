@@ -395,11 +395,8 @@ template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s
   tm.k = make_tma_4d(kv_desc(p.k, p.d, p.h_k, rows, slabs));
   tm.v = make_tma_4d(kv_desc(p.v, p.d, p.h_k, rows, slabs));
   auto kern = decode_kernel<HD, kBf16>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
-    attr_set = true;
-  }
+  static std::atomic<bool> smem_set[64];
+  ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   dim3 grid(p.num_splits > 1 ? p.num_splits : 1, p.h_k, p.b);
   profile_mark(0, true, s);
   kern<<<grid, kDThreads, L::kDynBytes, s>>>(p, tm);

@@ -788,11 +788,8 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false> v
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
     auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
-      attr_set = true;
-    }
+    static std::atomic<bool> smem_set[64];
+    ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
     dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
     int *dq_sem = nullptr;
     if (kDet) {                                 // one turn counter per dq_accum tile, stream-ordered scratch

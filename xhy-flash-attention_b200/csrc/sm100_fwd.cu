@@ -907,11 +907,8 @@ template <int HD, bool kBf16, bool kFM, bool kDrop> void launch_fwd(const Params
   const int num_tiles = p.b * p.h * num_m;
   if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
   auto kern = fwd_kernel<HD, kBf16, kFM, kDrop>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    FA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynBytes));
-    attr_set = true;
-  }
+  static std::atomic<bool> smem_set[64];
+  ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
   int *counter = nullptr;                          // stream-ordered scratch: the dynamic scheduler's tile counter
   if (kFM) {
