@@ -117,3 +117,44 @@ def test_dropout_tcgen05_path(fa, capi, sq, sk, d, h, hk, causal, dtype):
     check_2x("dv", dv, ref[4], pt[4])
     torch.testing.assert_close(out.float(), out_g.float(), atol=2e-2, rtol=2e-2)
     assert kind_bwd in (1, 2)
+
+
+def test_dropout_tcgen05_varlen_and_flashmask(fa, capi):
+    """The kDrop kernels on a packed batch and under a FlashMask: same seed through the generic kernels recovers the
+    mask (S_dmask), the oracle with that mask judges the fast path."""
+    torch.manual_seed(3)
+    lens, h, d, p = [77, 200, 130], 4, 64, 0.25
+    total = sum(lens)
+    qkv = torch.randn(total, 3, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    cu = torch.tensor([0, 77, 277, 407], device=DEV, dtype=torch.int32)
+    torch.manual_seed(11)
+    out = fa.flash_attn_varlen_qkvpacked_func(qkv, cu, max(lens), p, None, True)
+    assert capi.last_kernel_kind() == 2
+    g = torch.randn_like(out)
+    (dqkv,) = torch.autograd.grad(out, qkv, g)
+    assert capi.last_kernel_kind() == 2
+    torch.manual_seed(11)
+    _, _, S = fa.flash_attn_varlen_qkvpacked_func(qkv, cu, max(lens), p, None, True, True)
+    for i, n in enumerate(lens):
+        a, e = int(cu[i]), int(cu[i + 1])
+        keep = S[i:i + 1, :, :n, :n] >= 0
+        q, k, v = [qkv[a:e, j].unsqueeze(0) for j in range(3)]
+        ref = _ref_with_mask(q, k, v, g[a:e].unsqueeze(0), keep, True, p)
+        pt = _ref_with_mask(q, k, v, g[a:e].unsqueeze(0), keep, True, p, upcast=False, reorder_ops=True)
+        check_2x("out", out[a:e].unsqueeze(0), ref[0], pt[0])
+        for j, name in enumerate(("dq", "dk", "dv")):
+            check_2x(name, dqkv[a:e, j].unsqueeze(0), ref[2 + j], pt[2 + j])
+    # FlashMask (document mask) + dropout: fast path against the generic kernels with the same seed
+    s_, b = 640, 2
+    q = torch.randn(b, s_, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    k = torch.randn(b, s_, 2, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    v = torch.randn(b, s_, 2, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, s_, h, d, device=DEV, dtype=torch.bfloat16)
+    lts = orc.document_lt_start([200, 300, 140]).view(1, 1, s_).expand(b, 1, s_).contiguous().to(DEV)
+    res = []
+    for generic in (False, True):
+        torch.manual_seed(5)
+        o = fa.flash_attn_func(q, k, v, p, None, True, flashmask=(lts, None, None, None), _force_generic=generic)
+        res.append((o,) + torch.autograd.grad(o, (q, k, v), g))
+    for name, a_, b_ in zip(("out", "dq", "dk", "dv"), res[0], res[1]):
+        torch.testing.assert_close(a_.float(), b_.float(), atol=3e-2, rtol=3e-2, msg=lambda m: f"{name}: {m}")
