@@ -227,9 +227,16 @@ def test_decode_kernel_is_used(fa, capi):
     fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=4096, causal=True, num_splits=1)
     p_kind.append(capi.last_kernel_kind())
     assert p_kind == [3]
-    # more than 16 packed rows: outside the decode kernel's envelope, served by the generic kernel
+    # more than 16 packed rows: several 16-row tiles per (batch, kv-head), still the decode kernel
     q2 = torch.randn(2, 5, 32, 128, device=DEV, dtype=torch.bfloat16)
     fa.flash_attn_with_kvcache(q2, kc, vc, cache_seqlens=4096, causal=True, num_splits=1)
+    assert capi.last_kernel_kind() == 3
+    # more than 128 packed rows (chunked prefill over the cache): one pass of the tcgen05 forward
+    q3 = torch.randn(2, 64, 32, 128, device=DEV, dtype=torch.bfloat16)
+    fa.flash_attn_with_kvcache(q3, kc, vc, cache_seqlens=4096, causal=True)
+    assert capi.last_kernel_kind() == 2
+    # an explicit split of such a shape is honoured by the generic kernels
+    fa.flash_attn_with_kvcache(q3, kc, vc, cache_seqlens=4096, causal=True, num_splits=2)
     assert capi.last_kernel_kind() == 1
 
 
@@ -299,3 +306,26 @@ def test_flat_capi_dense_attn_mask(capi, mh, ms, causal):
     check_2x("dq", dq, ref[2], pt[2])
     check_2x("dk", dk, ref[3], pt[3])
     check_2x("dv", dv, ref[4], pt[4])
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,h,hk", [(5, 32, 8), (8, 16, 1), (33, 8, 8), (100, 4, 4), (300, 8, 2)])
+def test_kvcache_many_query_rows(fa, capi, sq, h, hk, causal):
+    """Speculative decoding / chunked prefill over a cache: 17..128 packed rows run as several 16-row tiles of the decode
+    kernel (kind 3), more than that as one tcgen05 forward pass with seqused_k and the bottom-right mask (kind 2)."""
+    torch.manual_seed(2)
+    b, sk, d = 3, 1500, 128
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16)
+    kc = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16)
+    vc = torch.randn(b, sk, hk, d, device=DEV, dtype=torch.bfloat16)
+    seqlens = torch.tensor([1500, 301, 777], device=DEV, dtype=torch.int32)
+    for i in range(b):
+        kc[i, int(seqlens[i]):] = float("nan"); vc[i, int(seqlens[i]):] = float("nan")
+    (ref, pt), lse_ref = _kvcache_ref(q, kc, vc, seqlens, causal)
+    for ns in (1, 0, 3):
+        out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=seqlens, causal=causal, num_splits=ns,
+                                              return_softmax_lse=True)
+        if ns == 1:   # (with splits the last launch is the combine kernel)
+            assert capi.last_kernel_kind() == (3 if sq * (h // hk) <= 128 else 2)
+        check_2x("out", out, ref, pt)
+        check_lse(lse, lse_ref)

@@ -74,7 +74,7 @@ def test_paged_append_crosses_pages(fa):
     check_lse(lse, lse_ref)
 
 
-@pytest.mark.parametrize("sq,kind", [(1, 3), (20, 1)])
+@pytest.mark.parametrize("sq,kind", [(1, 3), (20, 3), (40, 1)])
 def test_cache_batch_idx(fa, capi, sq, kind):
     torch.manual_seed(2)
     b, bk, sk, h, hk, d = 3, 7, 512, 16, 4, 128
@@ -96,7 +96,7 @@ def test_cache_batch_idx(fa, capi, sq, kind):
 
 
 @pytest.mark.parametrize("num_splits", [1, 4])
-@pytest.mark.parametrize("sq,kind", [(1, 3), (2, 3), (20, 1)])
+@pytest.mark.parametrize("sq,kind", [(1, 3), (2, 3), (20, 3), (70, 1)])
 @pytest.mark.parametrize("window", [(-1, -1), (100, 0)])
 def test_cache_leftpad(fa, capi, sq, kind, window, num_splits):
     torch.manual_seed(3)
@@ -168,7 +168,7 @@ def test_rotary_kernel_matches_oracle(capi):
                 assert torch.equal(y[..., rdim:], x[..., rdim:])
 
 
-@pytest.mark.parametrize("sq,kind", [(1, 3), (20, 1)])
+@pytest.mark.parametrize("sq,kind", [(1, 3), (20, 3), (70, 1)])
 @pytest.mark.parametrize("softcap", [0.0, 15.0])
 @pytest.mark.parametrize("alibi", [None, "h", "bh"])
 def test_softcap_alibi(fa, capi, sq, kind, softcap, alibi):

@@ -30,7 +30,8 @@ constexpr int kDT = 64;        // keys per pipeline stage
 constexpr int kDStages = 3;
 constexpr int kDWarps = 4;     // consumer warps
 constexpr int kDThreads = (kDWarps + 1) * 32;
-constexpr int kDRows = 16;     // packed query rows (seqlen_q * group size) one CTA can take
+constexpr int kDRows = 16;     // packed query rows (seqlen_q * group size) one CTA takes
+constexpr int kDMaxRows = 128; // packed rows per (batch, kv-head) served by this kernel, as ceil(rows / 16) row tiles
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -106,10 +107,14 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-  const int split = blockIdx.x, hk = blockIdx.y, bi = blockIdx.z;
+  // grid.x = splits x row tiles, row tile fastest: the CTAs that stream the same K/V range for different groups of 16
+  // packed rows are launched next to each other, so all but the first find it in L2
+  const int n_rt = (p.seqlen_q * (p.h / p.h_k) + kDRows - 1) / kDRows;
+  const int split = blockIdx.x / n_rt, rt = blockIdx.x % n_rt, hk = blockIdx.y, bi = blockIdx.z;
   const int g = p.h / p.h_k;
   const int sq = p.seqlen_q;
-  const int G = sq * g;                                       // packed rows in use (<= 16)
+  const int G = sq * g;                                       // packed rows of this (batch, kv-head); this CTA takes
+  const int row0 = rt * kDRows;                               // rows [row0, row0 + 16)
   // valid keys are the physical cache rows [leftpad, leftpad + sk) (csrc/flash_attn_v3/seqlen.h:73-80); everything
   // below the mask intervals works on PHYSICAL rows so that 64-key tiles never straddle a page
   const int leftpad = p.leftpad_k ? p.leftpad_k[bi] : 0;
@@ -132,7 +137,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
     split_hi = min(sk, (split + 1) * per);
   }
   int cta_lo = 0x7fffffff, cta_hi = 0;
-  for (int qi = 0; qi < sq; ++qi) {
+  for (int qi = row0 / g; qi < sq && qi * g < row0 + kDRows; ++qi) {   // the query rows this row tile touches
     int lo, hi;
     row_interval(p, qi, sq, sk, split_lo, split_hi, lo, hi);
     if (hi > lo) { cta_lo = min(cta_lo, lo + leftpad); cta_hi = max(cta_hi, hi + leftpad); }
@@ -171,7 +176,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   }
 
   // ======================= consumers =======================
-  const int quad = lane % 4, rA = lane / 4, rB = rA + 8;
+  const int quad = lane % 4, rA = row0 + lane / 4, rB = rA + 8, lA_ = lane / 4, lB_ = lA_ + 8;   // packed rows / tile-local rows
   // Q fragments (A operand, 16 packed rows x HD): packed row r -> query index r / g, head hk * g + r % g
   uint32_t qa[HD / 16][4];
   {
@@ -309,17 +314,18 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   float *sl = sm + kDWarps * kDRows;                           // [warp][16]
 #pragma unroll
   for (int nt = 0; nt < HD / 8; ++nt) {
-    *reinterpret_cast<float2 *>(so + (warp * kDRows + rA) * HD + nt * 8 + 2 * quad) = make_float2(o[nt][0], o[nt][1]);
-    *reinterpret_cast<float2 *>(so + (warp * kDRows + rB) * HD + nt * 8 + 2 * quad) = make_float2(o[nt][2], o[nt][3]);
+    *reinterpret_cast<float2 *>(so + (warp * kDRows + lA_) * HD + nt * 8 + 2 * quad) = make_float2(o[nt][0], o[nt][1]);
+    *reinterpret_cast<float2 *>(so + (warp * kDRows + lB_) * HD + nt * 8 + 2 * quad) = make_float2(o[nt][2], o[nt][3]);
   }
   if (quad == 0) {
-    sm[warp * kDRows + rA] = mA; sl[warp * kDRows + rA] = lA;
-    sm[warp * kDRows + rB] = mB; sl[warp * kDRows + rB] = lB;
+    sm[warp * kDRows + lA_] = mA; sl[warp * kDRows + lA_] = lA;
+    sm[warp * kDRows + lB_] = mB; sl[warp * kDRows + lB_] = lB;
   }
   named_bar_sync(1, kDWarps * 32);
   {
     const int row = threadIdx.x / 8, cg = threadIdx.x % 8;    // 16 rows x 8 column groups of HD / 8 floats
-    if (row < G) {
+    const int prow = row0 + row;                              // packed row
+    if (prow < G) {
       float M = -CUDART_INF_F;
 #pragma unroll
       for (int w = 0; w < kDWarps; ++w) M = fmaxf(M, sm[w * kDRows + row]);
@@ -331,7 +337,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
       }
       const bool empty = !(Lsum > 0.f);
       const float inv = empty ? 0.f : 1.f / Lsum;
-      const int qi = row / g, hq = hk * g + row % g;
+      const int qi = prow / g, hq = hk * g + prow % g;
       const float lse = empty ? -CUDART_INF_F : (M + log2f(Lsum)) * kLn2;
       constexpr int kPer = HD / 8;
       float acc[kPer];
@@ -397,7 +403,8 @@ template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s
   auto kern = decode_kernel<HD, kBf16>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
-  dim3 grid(p.num_splits > 1 ? p.num_splits : 1, p.h_k, p.b);
+  const int n_rt = ceil_div(p.seqlen_q * (p.h / p.h_k), kDRows);
+  dim3 grid((p.num_splits > 1 ? p.num_splits : 1) * n_rt, p.h_k, p.b);
   profile_mark(0, true, s);
   kern<<<grid, kDThreads, L::kDynBytes, s>>>(p, tm);
   profile_mark(0, false, s);
@@ -409,7 +416,7 @@ bool decode_supported(const Params &p) {
   if (p.force_generic) return false;
   if (p.d != 64 && p.d != 128) return false;
   if (p.cu_seqlens_q || p.cu_seqlens_k || p.lt_start) return false;
-  if (p.seqlen_q * (p.h / p.h_k) > kDRows) return false;
+  if (p.seqlen_q * (p.h / p.h_k) > kDMaxRows) return false;   // beyond that the tcgen05 forward is the better tool
   if (p.page_table && (p.page_size <= 0 || p.page_size % kDT != 0 || p.num_pages <= 0)) return false;
   const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
   if (!kv_ok(p.k, p.h_k, slabs) || !kv_ok(p.v, p.h_k, slabs)) return false;
@@ -421,9 +428,18 @@ bool decode_supported(const Params &p) {
 
 }  // namespace
 
-// kind 3 = the TMA-fed decode kernel, 1 = generic SIMT (shapes outside the envelope above)
+// kind 3 = the TMA-fed decode kernel, 2 = tcgen05 forward (many query rows, no split), 1 = generic SIMT
 void splitkv_fwd(const Params &p, cudaStream_t s) {
-  if (!decode_supported(p)) { generic_splitkv_fwd(p, s); return; }
+  if (!decode_supported(p)) {
+    // many query rows per kv-head (chunked prefill over a cache): the tcgen05 forward takes seqused_k and bottom-right
+    // masks itself; only the cache addressing modes / softcap / ALiBi and real splits need the generic kernels
+    const bool special = p.softcap > 0.f || p.alibi_slopes || p.page_table || p.kv_batch_idx || p.leftpad_k ||
+                         p.attn_mask || p.s_dmask || p.p_dropout > 0.f;
+    std::string why;
+    if (p.num_splits <= 1 && !p.force_generic && !special && sm100_fwd_supported(p, &why)) { sm100_fwd(p, s); return; }
+    generic_splitkv_fwd(p, s);
+    return;
+  }
   if (p.d == 64) {
     if (p.is_bf16) launch_decode<64, true>(p, s); else launch_decode<64, false>(p, s);
   } else {

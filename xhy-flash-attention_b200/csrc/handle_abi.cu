@@ -37,7 +37,7 @@ fa_b200_tensor tens(void *ptr, int64_t bs, int64_t rs, int64_t hs) {
 
 bool decode_shape(const Flash_fwd_params &h) {
   return h.cu_seqlens_q == nullptr && h.cu_seqlens_k == nullptr && h.lt_start_ptr == nullptr && h.h_k > 0 &&
-         h.seqlen_q * (h.h / h.h_k) <= 16 && (h.d == 64 || h.d == 128);
+         h.seqlen_q * (h.h / h.h_k) <= 128 && (h.d == 64 || h.d == 128);
 }
 
 // (h, total_q) <-> (b, h, max_seqlen_q): the v2/v3 surface keeps varlen LSE packed (flash_fwd_launch_template.h:161-164)
@@ -268,7 +268,7 @@ void run_bwd_handle(Flash_bwd_params *hp, cudaStream_t stream) {
 int num_splits_handle(const Flash_fwd_params &h) {
   const int num_sm = h.num_sm > 0 ? h.num_sm : fa::device_sm_count();
   if (h.h_k <= 0) return 1;
-  if (decode_shape(h)) return fa_b200_decode_num_splits(h.b, h.h_k, h.seqlen_k, num_sm);
+  if (decode_shape(h)) return fa_b200_decode_num_splits(h.b * ((h.seqlen_q * (h.h / h.h_k) + 15) / 16), h.h_k, h.seqlen_k, num_sm);
   return fa_b200_num_splits(h.b, h.h_k, h.seqlen_q * (h.h / h.h_k), h.seqlen_k, h.d, num_sm);
 }
 

@@ -523,6 +523,18 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
           const uint32_t vst = kv_it % kStages;
           mbar_wait(bar(B_KVFULL + vst), (kv_it / kStages) & 1);
           ++kv_it;
+          if (p.seqused_k != nullptr && cur.j * kBN + kBN > ti.sk) {
+            // KV cache: rows at or beyond the used length hold arbitrary bits (possibly NaN) and P = 0 times NaN would
+            // poison O -- zero the tail rows of this V tile (the reference zero-fills the V tail,
+            // flash_fwd_kernel.h:346-349).  A row is 128 bytes in each 64-column box, whatever the swizzle.
+            const int first = max(ti.sk - cur.j * kBN, 0);
+            const uint32_t vt = sbase + L::kKVOff + vst * L::kTileBytes;
+            for (int i = first * 8 + lane; i < kBN * 8; i += 32)
+#pragma unroll
+              for (int hf = 0; hf < kHalves; ++hf) sts128(vt + hf * kHalfBytes + i * 16, 0u, 0u, 0u, 0u);
+            fence_proxy_async_smem();
+            __syncwarp();
+          }
           uint32_t nkst = 0;
           bool next_waited = false;
 #pragma unroll

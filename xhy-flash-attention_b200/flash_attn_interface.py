@@ -572,10 +572,15 @@ def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None
         keep += [block_table, cache_batch_idx, cache_leftpad, alibi_slopes, seqused, q]
         if num_splits <= 0:
             num_sm = torch.cuda.get_device_properties(q.device).multi_processor_count
-            if sq * (h // h_k) <= 16 and d in (64, 128):   # the TMA-fed decode kernel (csrc/decode.cu)
-                num_splits = lib.fa_b200_decode_num_splits(b, h_k, sk, num_sm)
+            rows = sq * (h // h_k)                         # packed query rows per (batch, kv-head)
+            special = paged or cache_batch_idx is not None or cache_leftpad is not None or softcap != 0.0 or \
+                alibi_slopes is not None
+            if rows <= 128 and d in (64, 128):             # the TMA-fed decode kernel (csrc/decode.cu), 16 rows per CTA
+                num_splits = lib.fa_b200_decode_num_splits(b * ((rows + 15) // 16), h_k, sk, num_sm)
+            elif d <= 128 and not special:                 # chunked prefill over a cache: one tcgen05 forward pass
+                num_splits = 1
             else:
-                num_splits = lib.fa_b200_num_splits(b, h_k, sq * (h // h_k), sk, d, num_sm)
+                num_splits = lib.fa_b200_num_splits(b, h_k, rows, sk, d, num_sm)
         p.num_splits = num_splits
         if num_splits > 1:
             oaccum = torch.empty((num_splits, b, sq, h, d), dtype=torch.float32, device=q.device)
