@@ -256,14 +256,15 @@ def test_decode_window(fa, window, sq):
     check_lse(lse, lse_ref)
 
 
+@pytest.mark.parametrize("sk", [264, 261], ids=["sk264", "sk261_unaligned_rows"])
 @pytest.mark.parametrize("mh,ms", [(1, 1), (4, 1), (1, 200), (4, 200)])
 @pytest.mark.parametrize("causal", [False, True])
-def test_flat_capi_dense_attn_mask(capi, mh, ms, causal):
+def test_flat_capi_dense_attn_mask(capi, mh, ms, causal, sk):
     """flash_attn_fwd / flash_attn_bwd with the dense additive attn_mask of the flat ABI (csrc/capi/flash_attn.h:36-37):
     logits = scale * q.k + mask, mask (b, 1-or-h, 1-or-sq, sk) broadcast by h % mod / row % mod."""
     lib = capi.load()
     torch.manual_seed(0)
-    b, sq, sk, h, d = 2, 200, 264, 4, 64
+    b, sq, h, d = 2, 200, 4, 64
     q, g = [torch.randn(b, sq, h, d, device=DEV, dtype=torch.float16) for _ in range(2)]
     k, v = [torch.randn(b, sk, h, d, device=DEV, dtype=torch.float16) for _ in range(2)]
     bias = (torch.randn(b, mh, ms, sk, device=DEV) * 2).to(torch.float16)
@@ -287,6 +288,7 @@ def test_flat_capi_dense_attn_mask(capi, mh, ms, causal):
         C.c_bool(False), stream, C.c_uint64(0), C.c_uint64(0), vp(bias), dims, None, None, None, None, None, None,
         qr, kr, vr, qh, kh, vh, or_, oh, qb, kb, vb, ob)
     assert ok, capi.last_error()
+    assert capi.last_kernel_kind() == 2, "dense attn_mask forward did not take the tcgen05 kernel"
     (dqr, dqh, dqb), (dkr, dkh, dkb), (dvr, dvh, dvb), (gr, gh, gb) = st(dq), st(dk), st(dv), st(g)
     lib.flash_attn_bwd.restype = C.c_bool
     ok = lib.flash_attn_bwd(
@@ -296,6 +298,7 @@ def test_flat_capi_dense_attn_mask(capi, mh, ms, causal):
         C.c_uint64(0), vp(bias), dims, None, None, None, None, None, None,
         qr, kr, vr, qh, kh, vh, or_, oh, qb, kb, vb, ob, dqr, dkr, dvr, dqh, dkh, dvh, gr, gh, dqb, dkb, dvb, gb)
     assert ok, capi.last_error()
+    assert capi.last_kernel_kind() == 2, "dense attn_mask backward did not take the tcgen05 kernels"
     torch.cuda.synchronize()
     mask = orc.causal_mask_top_left(sq, sk).to(DEV) if causal else None
     bias_full = bias.float().expand(b, mh, sq if ms == 1 else ms, sk)

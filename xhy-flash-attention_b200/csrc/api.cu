@@ -80,10 +80,9 @@ void run_fwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
-  // dropout / return_softmax take the generic kernels (Philox per element); the tcgen05 kernels are dropout-free
-  // so do softcap / ALiBi and the KV-cache addressing modes outside the decode kernel (inference features)
-  // (dropout alone has its own tcgen05 instantiation; return_softmax needs the element-wise generic pass)
-  const bool special = p.s_dmask != nullptr || p.attn_mask != nullptr || p.softcap > 0.f ||
+  // return_softmax needs the element-wise generic pass; so do softcap / ALiBi and the KV-cache addressing modes outside
+  // the decode kernel (inference features).  Dropout and the dense attn_mask have tcgen05 instantiations of their own.
+  const bool special = p.s_dmask != nullptr || p.softcap > 0.f ||
                        p.alibi_slopes != nullptr || p.page_table != nullptr || p.kv_batch_idx != nullptr ||
                        p.leftpad_k != nullptr;
   if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
@@ -97,7 +96,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
-  const bool special = p.attn_mask != nullptr || p.softcap > 0.f || p.alibi_slopes != nullptr;   // dropout: kDrop kernels
+  const bool special = p.softcap > 0.f || p.alibi_slopes != nullptr;   // dropout / dense mask: own instantiations
   if (!p.force_generic && !special && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }

@@ -223,7 +223,7 @@ template <bool kFM> struct MCursor {
   }
 };
 
-template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop>
+template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop, bool kMask>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, int *__restrict__ dq_sem) {
   using L = BwdSmem<HD>;
@@ -538,6 +538,29 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
         uint32_t s[32];
         tmem_ld32(tS + c2 * 32, s);
         tmem_wait_ld();
+        if constexpr (kMask) {
+          // dense additive mask: this thread's key column, 32 query rows (lanes are consecutive columns, so every load
+          // of the warp is one contiguous run of 32 elements)
+          const T *mcol = (const T *)p.attn_mask +
+                          ((int64_t)t.bi * p.mask_head_mod + hq % p.mask_head_mod) * p.mask_seq_mod * (int64_t)p.seqlen_k + col;
+          const bool col_ok = col < p.seqlen_k;
+          // mask_seq_mod is 1 (one row for all queries) or the query length: no per-element integer division
+          const int64_t rstride = p.mask_seq_mod == 1 ? 0 : (int64_t)p.seqlen_k;
+          const int row_first = m0 + wg * 64 + c2 * 32;
+          uint16_t raw[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            int rowi = row_first + i;
+            if (rowi >= p.mask_seq_mod) rowi = p.mask_seq_mod == 1 ? 0 : rowi % p.mask_seq_mod;
+            raw[i] = col_ok ? *reinterpret_cast<const uint16_t *>(mcol + (int64_t)rowi * rstride) : (uint16_t)0;
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            T mv;
+            *reinterpret_cast<uint16_t *>(&mv) = raw[i];
+            s[i] = __float_as_uint(fmaf(to_float(mv), p.unscale_softmax, __uint_as_float(s[i])));
+          }
+        }
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           const float4 l4 = lds128(lse2_a + (c2 * 32 + i) * 4);
@@ -759,7 +782,7 @@ bool out_ok(const fa_b200_tensor &t) {
   return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
 }
 
-template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false> void launch_bwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, bool kMask = false> void launch_bwd(const Params &p, cudaStream_t s) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
@@ -787,7 +810,7 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false> v
   // 3. main kernel
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
-    auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop>;
+    auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop, kMask>;
     static std::atomic<bool> smem_set[64];
     ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
     dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
@@ -824,6 +847,7 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
   if (p.seqused_k) return no("seqused_k");
   if (p.deterministic && p.lt_start) return no("deterministic + FlashMask (key blocks skip query blocks irregularly)");
   if (p.deterministic && p.p_dropout > 0.f) return no("deterministic + dropout");
+  if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f || p.deterministic)) return no("dense attn_mask with FlashMask / dropout / deterministic");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -840,6 +864,11 @@ void sm100_bwd(const Params &p, cudaStream_t s) {
   if (p.deterministic && !fm) {   // ordered dQ accumulation: its own instantiation, the default kernels carry none of it
     if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, true>(p, s); else launch_bwd<64, false, false, true>(p, s); }
     else { if (p.is_bf16) launch_bwd<128, true, false, true>(p, s); else launch_bwd<128, false, false, true>(p, s); }
+    return;
+  }
+  if (p.attn_mask != nullptr) {   // dense additive mask (no FlashMask / dropout / deterministic with it)
+    if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, false, false, true>(p, s); else launch_bwd<64, false, false, false, false, true>(p, s); }
+    else { if (p.is_bf16) launch_bwd<128, true, false, false, false, true>(p, s); else launch_bwd<128, false, false, false, false, true>(p, s); }
     return;
   }
   if (p.p_dropout > 0.f) {        // dropout: its own instantiations as well

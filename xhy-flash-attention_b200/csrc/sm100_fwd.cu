@@ -337,7 +337,7 @@ template <bool kDyn> struct TileWalk {
   }
 };
 
-template <int HD, bool kBf16, bool kFM, bool kDrop>
+template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask>
 __global__ void __launch_bounds__(kThreads, 1)
 fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles,
            int *__restrict__ tile_counter) {
@@ -651,6 +651,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       const int shiftc = mc.bottom_right ? mc.shift : 0;
       const int r0 = ti.m0 + t * kBM;
       float m_ref = -CUDART_INF_F, l = 0.f;
+      // dense additive mask (kMask instantiation; the flat C ABI's attn_mask, csrc/flash_attn/src/softmax.h:360-379):
+      // logits = scale * (q.k + mask[b, h % head_mod, row % seq_mod, col] * unscale_softmax); a thread adds its row
+      const T *mask_row = nullptr;
+      if constexpr (kMask)
+        mask_row = (const T *)p.attn_mask + (((int64_t)ti.bi * p.mask_head_mod + ti.hq % p.mask_head_mod) * p.mask_seq_mod +
+                                             row % p.mask_seq_mod) * (int64_t)p.seqlen_k;
       seq.init(p, ti);
       Blk blk;
       uint32_t nb = 0;   // blocks of this Q tile processed so far
@@ -665,6 +671,30 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
         tmem_wait_ld();
         const int c0 = j * kBN;
+        if constexpr (kMask) {
+          // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
+          const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
+                              c0 + kBN <= p.seqlen_k;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              const int col = c0 + c * 32 + i;
+              if (vec_ok) {
+                const uint4 mv = *reinterpret_cast<const uint4 *>(mask_row + col);
+                const T *me = reinterpret_cast<const T *>(&mv);
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  s[c][i + e] = __float_as_uint(fmaf(to_float(me[e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+              } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (col + e < p.seqlen_k)
+                    s[c][i + e] = __float_as_uint(fmaf(to_float(mask_row[col + e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+              }
+            }
+          }
+        }
         const bool full = (c0 + kBN <= ti.sk) && (!mc.causal || c0 + kBN - 1 <= r0 + shiftc) &&
                           (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
                           (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) &&
@@ -905,7 +935,7 @@ bool tma_ok(const fa_b200_tensor &t, int heads, int batch) {
   return true;
 }
 
-template <int HD, bool kBf16, bool kFM, bool kDrop> void launch_fwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false> void launch_fwd(const Params &p, cudaStream_t s) {
   using L = FwdSmem<HD>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
@@ -918,7 +948,7 @@ template <int HD, bool kBf16, bool kFM, bool kDrop> void launch_fwd(const Params
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
   if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
-  auto kern = fwd_kernel<HD, kBf16, kFM, kDrop>;
+  auto kern = fwd_kernel<HD, kBf16, kFM, kDrop, kMask>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
@@ -942,6 +972,7 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
   auto no = [&](const char *w) { if (why) *why = w; return false; };
   if (p.d > 128) return no("head_size > 128");
   if (p.num_splits > 1) return no("split-KV");
+  if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f)) return no("dense attn_mask together with FlashMask / dropout");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if (p.cu_seqlens_q && !p.cu_seqlens_k) return no("cu_seqlens_q without cu_seqlens_k");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -959,6 +990,7 @@ namespace {
 template <int HD, bool kBf16> void dispatch_fwd(const Params &p, cudaStream_t s) {
   const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
   const bool drop = p.p_dropout > 0.f;
+  if (p.attn_mask != nullptr) { launch_fwd<HD, kBf16, false, false, true>(p, s); return; }   // dense mask: no FlashMask / dropout
   if (fm) { if (drop) launch_fwd<HD, kBf16, true, true>(p, s); else launch_fwd<HD, kBf16, true, false>(p, s); }
   else { if (drop) launch_fwd<HD, kBf16, false, true>(p, s); else launch_fwd<HD, kBf16, false, false>(p, s); }
 }
