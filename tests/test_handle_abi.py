@@ -211,12 +211,13 @@ def test_handle_decode_split_and_combine(fa):
 
 
 @pytest.mark.gpu
-def test_handle_softcap_fwd_bwd(fa):
+@pytest.mark.parametrize("s,h,hk,d,cap", [(200, 4, 2, 64, 8.0), (1024, 8, 2, 128, 30.0), (333, 4, 4, 96, 15.0)])
+def test_handle_softcap_fwd_bwd(fa, s, h, hk, d, cap):
     """softcap through the fa3 handle (csrc/flash_attn_v3/flash_api.cu:42,235): forward and backward, dS carries 1 - tanh^2."""
     from tests._util import check_2x
     lib = capi.load()
     torch.manual_seed(3)
-    b, s, h, hk, d, cap = 2, 200, 4, 2, 64, 8.0
+    b = 2
     dev = "cuda"
     q, g = [torch.randn(b, s, h, d, device=dev, dtype=torch.bfloat16) * 2 for _ in range(2)]
     k, v = [torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
@@ -238,11 +239,13 @@ def test_handle_softcap_fwd_bwd(fa):
                   f"{name}_head_stride": t.stride(2)})
     hb.call("run_mha_bwd", stream)
     torch.cuda.synchronize()
+    assert capi.last_kernel_kind() == 2, "softcap did not take the tcgen05 kernels"
     mask = orc.causal_mask_bottom_right(s, s).to(dev)
     ref = orc.attention_grads_ref(q, k, v, g, mask, softcap=cap)
     pt = orc.attention_grads_ref(q, k, v, g, mask, upcast=False, reorder_ops=True, softcap=cap)
     for name, got, i in (("out", o, 0), ("dq", dq, 2), ("dk", dk, 3), ("dv", dv, 4)):
-        check_2x(name, got, ref[i], pt[i], atol=1e-3)
+        check_2x(name, got, ref[i], pt[i], atol=3e-3)       # tanh.approx / lg2.approx: ~1e-3 relative
+    torch.testing.assert_close(lse, ref[1], atol=2e-2, rtol=1e-3)
     hf.close(); hb.close()
 
 

@@ -187,7 +187,8 @@ def test_softcap_alibi(fa, capi, sq, kind, softcap, alibi):
         slopes = torch.rand(b, h, device=DEV) * 0.3
     kw = dict(cache_seqlens=lens, causal=True, softcap=softcap, alibi_slopes=slopes)
     out, lse = fa.flash_attn_with_kvcache(q, kc, vc, num_splits=1, return_softmax_lse=True, **kw)
-    assert capi.last_kernel_kind() == kind
+    # many query rows: softcap alone has a tcgen05 instantiation, ALiBi needs the generic kernels
+    assert capi.last_kernel_kind() == (2 if (kind == 1 and alibi is None) else kind)
     ref, pt, lse_ref, _, _ = _ref_pair(q, kc, vc, **kw)
     # tanh.approx (decode kernel) is good to ~1e-3 relative; the 2x rule still holds with a small absolute slack
     check_2x("out", out, ref, pt, atol=3e-3 if softcap > 0 else 1e-4)

@@ -81,8 +81,8 @@ void run_fwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   // return_softmax needs the element-wise generic pass; so do softcap / ALiBi and the KV-cache addressing modes outside
-  // the decode kernel (inference features).  Dropout and the dense attn_mask have tcgen05 instantiations of their own.
-  const bool special = p.s_dmask != nullptr || p.softcap > 0.f ||
+  // the decode kernel (inference features).  Dropout, the dense attn_mask and softcap have tcgen05 instantiations.
+  const bool special = p.s_dmask != nullptr ||
                        p.alibi_slopes != nullptr || p.page_table != nullptr || p.kv_batch_idx != nullptr ||
                        p.leftpad_k != nullptr;
   if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
@@ -96,7 +96,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
-  const bool special = p.softcap > 0.f || p.alibi_slopes != nullptr;   // dropout / dense mask: own instantiations
+  const bool special = p.alibi_slopes != nullptr;   // dropout / dense mask / softcap: own instantiations
   if (!p.force_generic && !special && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }

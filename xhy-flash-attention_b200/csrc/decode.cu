@@ -433,7 +433,7 @@ void splitkv_fwd(const Params &p, cudaStream_t s) {
   if (!decode_supported(p)) {
     // many query rows per kv-head (chunked prefill over a cache): the tcgen05 forward takes seqused_k and bottom-right
     // masks itself; only the cache addressing modes / softcap / ALiBi and real splits need the generic kernels
-    const bool special = p.softcap > 0.f || p.alibi_slopes || p.page_table || p.kv_batch_idx || p.leftpad_k ||
+    const bool special = p.alibi_slopes || p.page_table || p.kv_batch_idx || p.leftpad_k ||
                          p.attn_mask || p.s_dmask || p.p_dropout > 0.f;
     std::string why;
     if (p.num_splits <= 1 && !p.force_generic && !special && sm100_fwd_supported(p, &why)) { sm100_fwd(p, s); return; }

@@ -58,6 +58,16 @@ enum BwdBar {
   BB_DP_FULL = 9, BB_DS_FULL = 10, BB_DQ_FULL = 11, BB_DQ_EMPTY = 12, BB_DKV_FULL = 13
 };
 
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2f(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float ex2f(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -223,7 +233,7 @@ template <bool kFM> struct MCursor {
   }
 };
 
-template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop, bool kMask>
+template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop, bool kMask, bool kCap>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, int *__restrict__ dq_sem) {
   using L = BwdSmem<HD>;
@@ -460,6 +470,8 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
     const int shift = t.sk - t.sq;
     const int shiftc = p.causal_bottom_right ? shift : 0;
     const float rp_drop = kDrop ? 1.f / (1.f - p.p_dropout) : 1.f;
+    const float pre_cap = kCap ? p.softmax_scale / p.softcap : 0.f, cap_log2 = kCap ? p.softcap * kLog2e : 0.f;
+    const float inv_cap_log2 = kCap ? 1.f / (p.softcap * kLog2e) : 0.f;
     MCursor<kFM> cur;
     cur.init(t);
     for (int it = 0; it < n_it; ++it) {
@@ -564,10 +576,17 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           const float4 l4 = lds128(lse2_a + (c2 * 32 + i) * 4);
-          pr[c2 * 32 + i + 0] = ex2f(fmaf(__uint_as_float(s[i + 0]), scale_log2, -l4.x));
-          pr[c2 * 32 + i + 1] = ex2f(fmaf(__uint_as_float(s[i + 1]), scale_log2, -l4.y));
-          pr[c2 * 32 + i + 2] = ex2f(fmaf(__uint_as_float(s[i + 2]), scale_log2, -l4.z));
-          pr[c2 * 32 + i + 3] = ex2f(fmaf(__uint_as_float(s[i + 3]), scale_log2, -l4.w));
+          if constexpr (kCap) {   // P = exp2(softcap * log2e * tanh(scale * s / softcap) - LSE * log2e)
+            pr[c2 * 32 + i + 0] = ex2f(fmaf(tanh_fast(__uint_as_float(s[i + 0]) * pre_cap), cap_log2, -l4.x));
+            pr[c2 * 32 + i + 1] = ex2f(fmaf(tanh_fast(__uint_as_float(s[i + 1]) * pre_cap), cap_log2, -l4.y));
+            pr[c2 * 32 + i + 2] = ex2f(fmaf(tanh_fast(__uint_as_float(s[i + 2]) * pre_cap), cap_log2, -l4.z));
+            pr[c2 * 32 + i + 3] = ex2f(fmaf(tanh_fast(__uint_as_float(s[i + 3]) * pre_cap), cap_log2, -l4.w));
+          } else {
+            pr[c2 * 32 + i + 0] = ex2f(fmaf(__uint_as_float(s[i + 0]), scale_log2, -l4.x));
+            pr[c2 * 32 + i + 1] = ex2f(fmaf(__uint_as_float(s[i + 1]), scale_log2, -l4.y));
+            pr[c2 * 32 + i + 2] = ex2f(fmaf(__uint_as_float(s[i + 2]), scale_log2, -l4.z));
+            pr[c2 * 32 + i + 3] = ex2f(fmaf(__uint_as_float(s[i + 3]), scale_log2, -l4.w));
+          }
         }
         if (!full) {
           const uint32_t mb = mbits[c2];
@@ -611,10 +630,20 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
             g2 = ((kb[c2] >> (i + 2)) & 1u) ? g2 * rp_drop : 0.f;
             g3 = ((kb[c2] >> (i + 3)) & 1u) ? g3 * rp_drop : 0.f;
           }
-          const float e0 = pr[c2 * 32 + i + 0] * (g0 - d4.x);
-          const float e1 = pr[c2 * 32 + i + 1] * (g1 - d4.y);
-          const float e2 = pr[c2 * 32 + i + 2] * (g2 - d4.z);
-          const float e3 = pr[c2 * 32 + i + 3] * (g3 - d4.w);
+          float e0 = pr[c2 * 32 + i + 0] * (g0 - d4.x);
+          float e1 = pr[c2 * 32 + i + 1] * (g1 - d4.y);
+          float e2 = pr[c2 * 32 + i + 2] * (g2 - d4.z);
+          float e3 = pr[c2 * 32 + i + 3] * (g3 - d4.w);
+          if constexpr (kCap) {
+            // d logit / d (scale * s) = 1 - tanh^2; tanh is recovered from P itself, tanh = (log2 P + LSE * log2e) /
+            // (softcap * log2e), clamped to [-1, 1] (P = 0 gives -inf), instead of holding 64 more registers
+            const float4 l4 = lds128(lse2_a + (c2 * 32 + i) * 4);
+            const float t0 = fminf(fmaxf((lg2f(pr[c2 * 32 + i + 0]) + l4.x) * inv_cap_log2, -1.f), 1.f);
+            const float t1 = fminf(fmaxf((lg2f(pr[c2 * 32 + i + 1]) + l4.y) * inv_cap_log2, -1.f), 1.f);
+            const float t2 = fminf(fmaxf((lg2f(pr[c2 * 32 + i + 2]) + l4.z) * inv_cap_log2, -1.f), 1.f);
+            const float t3 = fminf(fmaxf((lg2f(pr[c2 * 32 + i + 3]) + l4.w) * inv_cap_log2, -1.f), 1.f);
+            e0 *= fmaf(-t0, t0, 1.f); e1 *= fmaf(-t1, t1, 1.f); e2 *= fmaf(-t2, t2, 1.f); e3 *= fmaf(-t3, t3, 1.f);
+          }
           pk[i / 2] = pack2<kBf16>(e0, e1);
           pk[i / 2 + 1] = pack2<kBf16>(e2, e3);
         }
@@ -782,7 +811,7 @@ bool out_ok(const fa_b200_tensor &t) {
   return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride % 8 == 0 && t.head_stride % 8 == 0 && t.batch_stride % 8 == 0;
 }
 
-template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, bool kMask = false> void launch_bwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, bool kMask = false, bool kCap = false> void launch_bwd(const Params &p, cudaStream_t s) {
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
@@ -810,7 +839,7 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
   // 3. main kernel
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
-    auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop, kMask>;
+    auto kern = bwd_kernel<HD, kBf16, kFM, kDet, kDrop, kMask, kCap>;
     static std::atomic<bool> smem_set[64];
     ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
     dim3 grid(ceil_div(p.seqlen_k, kB), p.dkv_expanded ? p.h : p.h_k, p.b);
@@ -848,6 +877,7 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
   if (p.deterministic && p.lt_start) return no("deterministic + FlashMask (key blocks skip query blocks irregularly)");
   if (p.deterministic && p.p_dropout > 0.f) return no("deterministic + dropout");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f || p.deterministic)) return no("dense attn_mask with FlashMask / dropout / deterministic");
+  if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.deterministic || p.attn_mask)) return no("softcap with FlashMask / dropout / deterministic / attn_mask");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -869,6 +899,11 @@ void sm100_bwd(const Params &p, cudaStream_t s) {
   if (p.attn_mask != nullptr) {   // dense additive mask (no FlashMask / dropout / deterministic with it)
     if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, false, false, true>(p, s); else launch_bwd<64, false, false, false, false, true>(p, s); }
     else { if (p.is_bf16) launch_bwd<128, true, false, false, false, true>(p, s); else launch_bwd<128, false, false, false, false, true>(p, s); }
+    return;
+  }
+  if (p.softcap > 0.f) {          // softcap (no FlashMask / dropout / deterministic / dense mask with it)
+    if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, false, false, false, true>(p, s); else launch_bwd<64, false, false, false, false, false, true>(p, s); }
+    else { if (p.is_bf16) launch_bwd<128, true, false, false, false, false, true>(p, s); else launch_bwd<128, false, false, false, false, false, true>(p, s); }
     return;
   }
   if (p.p_dropout > 0.f) {        // dropout: its own instantiations as well

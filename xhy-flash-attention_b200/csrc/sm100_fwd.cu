@@ -337,7 +337,7 @@ template <bool kDyn> struct TileWalk {
   }
 };
 
-template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask>
+template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask, bool kCap>
 __global__ void __launch_bounds__(kThreads, 1)
 fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles,
            int *__restrict__ tile_counter) {
@@ -619,7 +619,12 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
     const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
     const uint32_t tS = tmem + lane_base + t * kBN;
     const uint32_t tO = tmem + lane_base + 2 * kBN + t * HD;
-    const float scale_log2 = p.softmax_scale * kLog2e;
+    // softcap (kCap instantiation): logits = softcap * tanh(scale * s / softcap), applied to S right after the load and
+    // before any mask (csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:537-556,1064-1067); from there on the values
+    // are tanh outputs and the "scale" of the softmax is softcap
+    const float scale_nat = kCap ? p.softcap : p.softmax_scale;
+    const float scale_log2 = scale_nat * kLog2e;
+    const float pre_cap = kCap ? p.softmax_scale / p.softcap : 0.f;
     uint32_t scnt = 0, ocnt = 0;
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     BlockSeq<kFM> seq;
@@ -671,6 +676,16 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
         for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
         tmem_wait_ld();
         const int c0 = j * kBN;
+        if constexpr (kCap) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float y;
+              asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(s[c][i]) * pre_cap));
+              s[c][i] = __float_as_uint(y);
+            }
+        }
         if constexpr (kMask) {
           // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
           const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
@@ -882,7 +897,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
       }
       tc_fence_before();
       if (row < ti.sq)
-        lse_ptr[row] = nonempty ? (m_ref * p.softmax_scale + __logf(l))
+        lse_ptr[row] = nonempty ? (m_ref * scale_nat + __logf(l))
                                  : (p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F);
       named_bar_sync(1 + t, kBM);
       {
@@ -935,7 +950,7 @@ bool tma_ok(const fa_b200_tensor &t, int heads, int batch) {
   return true;
 }
 
-template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false> void launch_fwd(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCap = false> void launch_fwd(const Params &p, cudaStream_t s) {
   using L = FwdSmem<HD>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
@@ -948,7 +963,7 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false> void lau
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
   if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
-  auto kern = fwd_kernel<HD, kBf16, kFM, kDrop, kMask>;
+  auto kern = fwd_kernel<HD, kBf16, kFM, kDrop, kMask, kCap>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
@@ -973,6 +988,7 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
   if (p.d > 128) return no("head_size > 128");
   if (p.num_splits > 1) return no("split-KV");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f)) return no("dense attn_mask together with FlashMask / dropout");
+  if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.attn_mask)) return no("softcap together with FlashMask / dropout / attn_mask");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if (p.cu_seqlens_q && !p.cu_seqlens_k) return no("cu_seqlens_q without cu_seqlens_k");
   if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
@@ -991,6 +1007,7 @@ template <int HD, bool kBf16> void dispatch_fwd(const Params &p, cudaStream_t s)
   const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
   const bool drop = p.p_dropout > 0.f;
   if (p.attn_mask != nullptr) { launch_fwd<HD, kBf16, false, false, true>(p, s); return; }   // dense mask: no FlashMask / dropout
+  if (p.softcap > 0.f) { launch_fwd<HD, kBf16, false, false, false, true>(p, s); return; }       // softcap: likewise
   if (fm) { if (drop) launch_fwd<HD, kBf16, true, true>(p, s); else launch_fwd<HD, kBf16, true, false>(p, s); }
   else { if (drop) launch_fwd<HD, kBf16, false, true>(p, s); else launch_fwd<HD, kBf16, false, false>(p, s); }
 }
