@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 3
+#define FA_B200_ABI_VERSION 4
 
 /* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
  * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
@@ -107,6 +107,16 @@ typedef struct fa_b200_params {
   float   softcap;                /* > 0: logits = softcap * tanh(scale * q.k / softcap)  (before masks and ALiBi) */
   const float *alibi_slopes;      /* (h) or (b, h) fp32 or NULL: logits -= slope * |col - (row + seqlen_k - seqlen_q)| */
   int64_t alibi_batch_stride;     /* 0 for (h) */
+
+  /* ---- dense additive bias with its gradient (ABI v4; the legacy flash_attn_*_with_bias_and_mask symbols:
+   *      csrc/flash_attn_with_bias_and_mask/src/fmha/gmem_tile.h:735-760,880-925, softmax.h:480-498) ---- */
+  const void *attn_bias;          /* (bias_batch_mod, h, bias_rows, seqlen_k) in the element type, or NULL:
+                                     logits += bias[b % bias_batch_mod, h, row, col] * unscale_softmax */
+  int32_t bias_batch_mod;         /* 1 (shared by the batch) or b */
+  int32_t bias_rows;              /* row count of attn_bias / ds_out (the unrounded max query length) */
+  void   *ds_out;                 /* backward, optional: (b, h, bias_rows, seqlen_k) in the element type, receives
+                                     dS = P * (dP - dPsum) for every visible (row, col); the caller zero-fills it and
+                                     reduces it over the batch when the bias is shared.  Generic kernels only. */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

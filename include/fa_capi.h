@@ -120,8 +120,14 @@ bool calc_reduced_attn_scores(
     int q_head_stride, int k_head_stride, int o_head_stride,
     int q_batch_stride, int k_batch_stride, int o_batch_stride);
 
-/* replaces csrc/capi/flash_attn.h:249-311 (legacy FA1 bias+mask path).  Exported for link
- * compatibility; this build reports "not supported" through the error string. */
+/* replaces csrc/capi/flash_attn.h:249-311 (legacy FA1 path with an additive mask and an additive bias + its gradient;
+ * csrc/flash_attn_with_bias_and_mask/flash_attn_with_bias_mask.cu:268-541).  Packed (total, h, d) tensors + cu_seqlens,
+ * no GQA, no causal; attn_mask is (b, 1|h, 1|max_seqlen_q, max_seqlen_k), attn_bias (n, h, max_seqlen_q, max_seqlen_k)
+ * read as bias[b % n]; softmax_scale must be 1 when either is given; softmax_lse / dsoftmax are
+ * (b, h, round_up(max_seqlen_q, 16)) fp32; dbias is (b, h, max_seqlen_q, max_seqlen_k) in the element type, zero-filled
+ * by the call; out == NULL only reports *workspace_size (0: no workspace is needed, workspace_ptr is ignored).
+ * Mask / bias rows are strided by max_seqlen_k (the reference strides by each sequence's own length, the same thing
+ * for the uniform batches its callers pass). */
 bool flash_attn_fwd_with_bias_and_mask(
     const void *q, const void *k, const void *v, void *out,
     const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k,

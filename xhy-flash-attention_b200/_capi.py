@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
 LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
-FA_B200_ABI_VERSION = 3
+FA_B200_ABI_VERSION = 4
 
 
 class Tensor(C.Structure):
@@ -53,6 +53,7 @@ class Params(C.Structure):
         ("kv_batch_idx", C.c_void_p), ("b_k", C.c_int32),
         ("leftpad_k", C.c_void_p), ("softcap", C.c_float),
         ("alibi_slopes", C.c_void_p), ("alibi_batch_stride", C.c_int64),
+        ("attn_bias", C.c_void_p), ("bias_batch_mod", C.c_int32), ("bias_rows", C.c_int32), ("ds_out", C.c_void_p),
     ]
 
 

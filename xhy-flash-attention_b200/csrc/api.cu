@@ -63,6 +63,7 @@ static void check_common(const Params &p) {
   FA_CHECK(device_cc_major() >= 10, "libflashattn_b200 needs a Blackwell (sm_100a) device");
   if (p.attn_mask) FA_CHECK(p.mask_head_mod > 0 && p.mask_seq_mod > 0, "attn_mask needs mask_head_mod and mask_seq_mod");
   FA_CHECK(p.softcap >= 0.f, "softcap must be >= 0");
+  if (p.attn_bias || p.ds_out) FA_CHECK(p.bias_batch_mod > 0 && p.bias_rows > 0, "attn_bias / ds_out need bias_batch_mod and bias_rows");
   if (p.page_table) {
     FA_CHECK(p.page_size > 0 && p.num_pages > 0 && p.page_table_batch_stride > 0, "page_table needs page_size, num_pages and its batch stride");
     FA_CHECK(!p.kv_batch_idx, "page_table and kv_batch_idx are exclusive");
@@ -84,7 +85,7 @@ void run_fwd(const Params &p, cudaStream_t s) {
   // the decode kernel (inference features).  Dropout, the dense attn_mask and softcap have tcgen05 instantiations.
   const bool special = p.s_dmask != nullptr ||
                        p.alibi_slopes != nullptr || p.page_table != nullptr || p.kv_batch_idx != nullptr ||
-                       p.leftpad_k != nullptr;
+                       p.leftpad_k != nullptr || p.attn_bias != nullptr;
   if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
   else generic_fwd(p, s);
 }
@@ -96,7 +97,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
-  const bool special = p.alibi_slopes != nullptr;   // dropout / dense mask / softcap: own instantiations
+  const bool special = p.alibi_slopes != nullptr || p.attn_bias != nullptr || p.ds_out != nullptr;   // dropout / dense mask / softcap: own instantiations
   if (!p.force_generic && !special && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
   else generic_bwd(p, s);
 }

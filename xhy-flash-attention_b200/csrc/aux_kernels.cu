@@ -245,6 +245,10 @@ lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int
   if (lane == 0) lse[li] = ln;
 }
 
+__global__ void __launch_bounds__(256) fill_f32_kernel(float *dst, float value, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) dst[i] = value;
+}
+
 }  // namespace
 
 void combine_fwd(const Params &p, cudaStream_t s) {
@@ -347,6 +351,14 @@ void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, i
     if (is_bf16) lse_merge_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 128, 0, s>>>((__nv_bfloat16 *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
     else lse_merge_kernel<__half, __half><<<grid, 128, 0, s>>>((__half *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
   }
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void fill_f32(float *dst, float value, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  const int64_t blocks = (n + 255) / 256;
+  fill_f32_kernel<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, s>>>(dst, value, n);
   FA_CUDA(cudaGetLastError());
   note_launch(1);
 }

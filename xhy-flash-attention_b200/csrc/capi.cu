@@ -73,6 +73,47 @@ void set_flashmask(Params &p, const void *downstart, const int64_t *dims, const 
   p.flashmask_maxmin = (int32_t *)const_cast<void *>(maxmin);
 }
 
+// shared argument translation of the two FA1 symbols (flash_attn_with_bias_mask.cu:301-350,433-491)
+Params fa1_params(int batch_size, int num_heads, int head_size, int max_seqlen_q_, int max_seqlen_k_, int total_q,
+                  int total_k, float p_dropout, float softmax_scale, bool is_bf16, uint64_t seed, uint64_t offset,
+                  const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, const void *attn_mask, const void *attn_bias,
+                  const int64_t *mask_dims, const int64_t *bias_dims) {
+  FA_CHECK(batch_size > 0, "batch_size must be positive");
+  FA_CHECK(head_size % 8 == 0 && head_size <= 128, "head_size must be a multiple of 8 and <= 128");
+  FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
+  FA_CHECK(p_dropout >= 0.f && p_dropout < 1.f, "p_dropout must be in [0, 1)");
+  if (attn_bias || attn_mask)   // the reference adds both before its own scaling and requires scale 1 (ibid.:344-347)
+    FA_CHECK(softmax_scale == 1.0f, "softmax_scale must be 1 when attn_bias or attn_mask is given");
+  const int sq_r = (max_seqlen_q_ + 15) / 16 * 16;   // row stride of softmax_lse / dsoftmax (ibid.:318)
+  Params p = base_params(batch_size, sq_r, max_seqlen_k_, sq_r, (max_seqlen_k_ + 127) / 128 * 128, num_heads, num_heads,
+                         head_size, (head_size + 31) / 32 * 32, softmax_scale, false, is_bf16);
+  p.total_q = total_q; p.total_k = total_k;
+  p.cu_seqlens_q = cu_seqlens_q; p.cu_seqlens_k = cu_seqlens_k;
+  p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
+  p.lse_empty_is_neg_inf = 1;                        // FA1 leaves -inf for rows without keys (ibid.:355)
+  p.force_generic = 1;
+  p.unscale_softmax = 1.f;
+  p.bias_rows = max_seqlen_q_;
+  p.bias_batch_mod = 1;
+  if (attn_mask) {
+    FA_CHECK(mask_dims != nullptr, "mask_dims must be given with attn_mask");
+    FA_CHECK(mask_dims[0] == batch_size && mask_dims[3] == max_seqlen_k_, "mask_dims must be (batch, 1 or heads, 1 or max_seqlen_q, max_seqlen_k)");
+    FA_CHECK(mask_dims[1] == 1 || mask_dims[1] == num_heads, "mask_dims[1] must be 1 or num_heads");
+    FA_CHECK(mask_dims[2] == 1 || mask_dims[2] == max_seqlen_q_, "mask_dims[2] must be 1 or max_seqlen_q");
+    p.attn_mask = attn_mask;
+    p.mask_head_mod = (int)mask_dims[1]; p.mask_seq_mod = (int)mask_dims[2];
+  }
+  if (attn_bias) {
+    FA_CHECK(bias_dims != nullptr, "bias_dims must be given with attn_bias");
+    FA_CHECK(bias_dims[1] == num_heads, "bias_dims[1] must equal num_heads");
+    FA_CHECK(bias_dims[0] >= 1, "bias_dims[0] must be positive");   // batch element b reads bias[b % bias_dims[0]]
+    FA_CHECK(bias_dims[2] == max_seqlen_q_ && bias_dims[3] == max_seqlen_k_, "bias_dims must end in (max_seqlen_q, max_seqlen_k)");
+    p.attn_bias = attn_bias;
+    p.bias_batch_mod = (int)bias_dims[0];
+  }
+  return p;
+}
+
 }  // namespace
 
 #define FA_BEGIN try {
@@ -253,21 +294,80 @@ bool calc_reduced_attn_scores(
   FA_END
 }
 
+// ---- legacy FA1 symbols: packed varlen tensors (total, h, d), no GQA, no causal, additive mask and bias, dbias ----
+// csrc/flash_attn_with_bias_and_mask/flash_attn_with_bias_mask.cu:268-397 (fwd), 400-541 (bwd).  softmax_lse and
+// dsoftmax are (b, h, round_up(max_seqlen_q, 16)) fp32 as there.  The reference strides mask / bias rows by each
+// sequence's own length, which describes a dense tensor only when all lengths equal the maximum; here the row stride
+// is mask_dims[3] / bias_dims[3] = max_seqlen_k, identical for uniform batches and well defined for ragged ones.
+// These run on the generic kernels (the bias path reads and writes O(s^2) tensors; it is HBM-bound by construction).
 bool flash_attn_fwd_with_bias_and_mask(
-    const void *, const void *, const void *, void *, const int32_t *, const int32_t *, int, int, int, int, int, int,
-    int, float, float, bool, bool, int, void *, void *, uint64_t *, cudaStream_t, uint64_t, uint64_t, const void *,
-    const void *, const int64_t *, const int64_t *) {
-  flash_attn_set_error("flash_attn_fwd_with_bias_and_mask (legacy FA1 bias+mask path) is not supported by libflashattn_b200");
-  return false;
+    const void *q, const void *k, const void *v, void *out, const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k,
+    int total_q, int total_k, int batch_size, int num_heads, int head_size, int max_seqlen_q_, int max_seqlen_k_,
+    float p_dropout, float softmax_scale, bool zero_tensors, bool is_bf16, int num_splits, void *softmax_lse_ptr,
+    void *workspace_ptr, uint64_t *workspace_size, cudaStream_t stream, uint64_t seed, uint64_t offset,
+    const void *attn_mask, const void *attn_bias, const int64_t *mask_dims, const int64_t *bias_dims) {
+  FA_BEGIN
+  if (out == nullptr) {                     // workspace query (flash_attn_with_bias_mask.cu:321-330): none needed here
+    FA_CHECK(workspace_size != nullptr, "workspace_size must be given for the workspace query");
+    *workspace_size = 0;
+    return true;
+  }
+  Params p = fa1_params(batch_size, num_heads, head_size, max_seqlen_q_, max_seqlen_k_, total_q, total_k, p_dropout,
+                        softmax_scale, is_bf16, seed, offset, cu_seqlens_q, cu_seqlens_k, attn_mask, attn_bias,
+                        mask_dims, bias_dims);
+  p.q = tensor(q, 0, num_heads * head_size, head_size);
+  p.k = tensor(k, 0, num_heads * head_size, head_size);
+  p.v = tensor(v, 0, num_heads * head_size, head_size);
+  p.o = tensor(out, 0, num_heads * head_size, head_size);
+  FA_CHECK(softmax_lse_ptr != nullptr, "softmax_lse_ptr must be given");
+  p.softmax_lse = (float *)softmax_lse_ptr;
+  if (zero_tensors) {                       // flash_attn_with_bias_mask.cu:353-356
+    FA_CUDA(cudaMemsetAsync(out, 0, (size_t)total_q * num_heads * head_size * 2, stream));
+    fa::fill_f32((float *)softmax_lse_ptr, -INFINITY, (int64_t)batch_size * num_heads * p.seqlen_q, stream);
+  }
+  (void)workspace_ptr; (void)num_splits;
+  fa::run_fwd(p, stream);
+  FA_END
 }
 
 bool flash_attn_bwd_with_bias_and_mask(
-    const void *, const void *, const void *, void *, void *, void *, const void *, const void *, const int32_t *,
-    const int32_t *, int, int, int, int, int, int, int, float, float, bool, bool, int, const void *, void *, void *,
-    void *, uint64_t *, cudaStream_t, uint64_t, uint64_t, const void *, const void *, const int64_t *,
-    const int64_t *) {
-  flash_attn_set_error("flash_attn_bwd_with_bias_and_mask (legacy FA1 bias+mask path) is not supported by libflashattn_b200");
-  return false;
+    const void *q, const void *k, const void *v, void *dq, void *dk, void *dv, const void *out, const void *dout,
+    const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, int total_q, int total_k, int batch_size, int num_heads,
+    int head_size, int max_seqlen_q_, int max_seqlen_k_, float p_dropout, float softmax_scale, bool zero_tensors,
+    bool is_bf16, int num_splits, const void *softmax_lse_ptr, void *dsoftmax_ptr, void *dbias_ptr, void *workspace_ptr,
+    uint64_t *workspace_size, cudaStream_t stream, uint64_t seed, uint64_t offset, const void *attn_mask,
+    const void *attn_bias, const int64_t *mask_dims, const int64_t *bias_dims) {
+  FA_BEGIN
+  if (out == nullptr) {                     // workspace query (flash_attn_with_bias_mask.cu:456-468)
+    FA_CHECK(workspace_size != nullptr, "workspace_size must be given for the workspace query");
+    *workspace_size = 0;
+    return true;
+  }
+  Params p = fa1_params(batch_size, num_heads, head_size, max_seqlen_q_, max_seqlen_k_, total_q, total_k, p_dropout,
+                        softmax_scale, is_bf16, seed, offset, cu_seqlens_q, cu_seqlens_k, attn_mask, attn_bias,
+                        mask_dims, bias_dims);
+  FA_CHECK(dq && dk && dv && dout && softmax_lse_ptr && dsoftmax_ptr, "backward tensors must be given");
+  const int rs = num_heads * head_size;
+  p.q = tensor(q, 0, rs, head_size); p.k = tensor(k, 0, rs, head_size); p.v = tensor(v, 0, rs, head_size);
+  p.o = tensor(out, 0, rs, head_size); p.dout = tensor(dout, 0, rs, head_size);
+  p.dq = tensor(dq, 0, rs, head_size); p.dk = tensor(dk, 0, rs, head_size); p.dv = tensor(dv, 0, rs, head_size);
+  p.softmax_lse = (float *)const_cast<void *>(softmax_lse_ptr);
+  p.softmax_d = (float *)dsoftmax_ptr;
+  p.dkv_expanded = 1;
+  if (attn_bias) {                          // flash_attn_with_bias_mask.cu:471-476: dbias is (b, h, sq, sk), zero-filled
+    FA_CHECK(dbias_ptr != nullptr, "dbias_ptr must be given with attn_bias");
+    FA_CUDA(cudaMemsetAsync(dbias_ptr, 0, (size_t)batch_size * num_heads * max_seqlen_q_ * max_seqlen_k_ * 2, stream));
+    p.ds_out = dbias_ptr;
+  }
+  if (zero_tensors) {                       // flash_attn_with_bias_mask.cu:493-498
+    FA_CUDA(cudaMemsetAsync(dq, 0, (size_t)total_q * rs * 2, stream));
+    FA_CUDA(cudaMemsetAsync(dk, 0, (size_t)total_k * rs * 2, stream));
+    FA_CUDA(cudaMemsetAsync(dv, 0, (size_t)total_k * rs * 2, stream));
+    FA_CUDA(cudaMemsetAsync(dsoftmax_ptr, 0, (size_t)batch_size * num_heads * p.seqlen_q * 4, stream));
+  }
+  (void)workspace_ptr; (void)num_splits;
+  fa::run_bwd(p, stream);
+  FA_END
 }
 
 }  // extern "C"

@@ -64,10 +64,17 @@ __device__ __forceinline__ float dot_row(const float *__restrict__ a, const T *_
 // csrc/flash_attn/src/softmax.h:360-379 adds it to the unscaled score, row offset as flash_fwd_kernel.h:1104-1107
 template <typename T>
 __device__ __forceinline__ float mask_term(const Params &p, int bi, int hq, int row, int col) {
-  if (p.attn_mask == nullptr) return 0.f;
-  const int64_t off = ((((int64_t)bi * p.mask_head_mod + hq % p.mask_head_mod) * p.mask_seq_mod + row % p.mask_seq_mod) *
-                       (int64_t)p.seqlen_k) + col;
-  return to_f(((const T *)p.attn_mask)[off]) * p.unscale_softmax;
+  float t = 0.f;
+  if (p.attn_mask != nullptr) {
+    const int64_t off = ((((int64_t)bi * p.mask_head_mod + hq % p.mask_head_mod) * p.mask_seq_mod + row % p.mask_seq_mod) *
+                         (int64_t)p.seqlen_k) + col;
+    t = to_f(((const T *)p.attn_mask)[off]);
+  }
+  if (p.attn_bias != nullptr) {   // (b % bias_batch_mod, h, row, col): fmha/gmem_tile.h:747-752 of the FA1 tree
+    const int64_t off = ((((int64_t)(bi % p.bias_batch_mod) * p.h + hq) * p.bias_rows + row) * (int64_t)p.seqlen_k) + col;
+    t += to_f(((const T *)p.attn_bias)[off]);
+  }
+  return t * p.unscale_softmax;
 }
 
 struct Seq {
@@ -307,6 +314,9 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dq_kernel(const Params p)
       float dp = dot_row(g_s[warp], vbase + (int64_t)col * p.v.row_stride, d);
       if (drop) dp = dropout_keep(dc, col) ? dp * rp : 0.f;   // dP = keep / p_keep * (dO . V)
       ds = pij * (dp - dsum) * dfac;
+      // gradient of the additive bias, one element per visible score (fmha/gmem_tile.h:880-925 of the FA1 tree)
+      if (p.ds_out != nullptr)
+        ((T *)p.ds_out)[((((int64_t)bi * p.h + hq) * p.bias_rows + row) * (int64_t)p.seqlen_k) + col] = from_f<T>(ds * p.unscale_softmax);
     }
     const int nj = min(32, hi - j0);
     for (int jj = 0; jj < nj; ++jj) {
