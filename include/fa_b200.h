@@ -117,6 +117,9 @@ typedef struct fa_b200_params {
   void   *ds_out;                 /* backward, optional: (b, h, bias_rows, seqlen_k) in the element type, receives
                                      dS = P * (dP - dPsum) for every visible (row, col); the caller zero-fills it and
                                      reduces it over the batch when the bias is shared.  Generic kernels only. */
+  int32_t dq_accum_batch_major;   /* packed varlen backward: 1 = dq_accum is sized (b, h, seqlen_q_rounded, d_rounded) as
+                                     the flat varlen symbol's callers allocate it (csrc/flash_attn/flash_api.cpp:836-838);
+                                     0 = the compact h * floor((total_q + 128 * b) / 128) tiles */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

@@ -73,6 +73,22 @@ void set_flashmask(Params &p, const void *downstart, const int64_t *dims, const 
   p.flashmask_maxmin = (int32_t *)const_cast<void *>(maxmin);
 }
 
+// The flat varlen symbols carry no total row counts, which the TMA descriptors of the tcgen05 kernels need as tensor
+// extents (the tail tile of the last sequence relies on the out-of-bounds zero fill).  Read cu_seqlens[b] back (8 bytes,
+// one stream synchronisation); while the stream is being captured into a CUDA graph that is not possible and the call
+// stays on the generic kernels.  Callers that know the totals use fa_b200_fwd / the handle ABI (total_q / total_k).
+void resolve_varlen_totals(Params &p, cudaStream_t stream) {
+  if (p.varlen_padded_input || p.total_q >= 0) return;
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  FA_CUDA(cudaStreamIsCapturing(stream, &st));
+  if (st != cudaStreamCaptureStatusNone) return;
+  int32_t tq = -1, tk = -1;
+  FA_CUDA(cudaMemcpyAsync(&tq, p.cu_seqlens_q + p.b, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  FA_CUDA(cudaMemcpyAsync(&tk, p.cu_seqlens_k + p.b, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  FA_CUDA(cudaStreamSynchronize(stream));
+  p.total_q = tq; p.total_k = tk;
+}
+
 // shared argument translation of the two FA1 symbols (flash_attn_with_bias_mask.cu:301-350,433-491)
 Params fa1_params(int batch_size, int num_heads, int head_size, int max_seqlen_q_, int max_seqlen_k_, int total_q,
                   int total_k, float p_dropout, float softmax_scale, bool is_bf16, uint64_t seed, uint64_t offset,
@@ -176,10 +192,12 @@ bool flash_attn_varlen_fwd(
     int v_head_stride, int o_row_stride, int o_head_stride, int q_batch_stride, int k_batch_stride, int v_batch_stride,
     int o_batch_stride, bool varlen_padded_input) {
   FA_BEGIN
-  unsupported(attn_mask != nullptr, "dense attn_mask");
   FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
   Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
                          num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  // mask rows are local to each sequence, its row stride is max_seqlen_k (flash_fwd_kernel.h:1104-1107 with the varlen
+  // params.seqlen_k = max_seqlen_k, csrc/capi/flash_attn.cu:730-733)
+  set_attn_mask(p, attn_mask, (const int64_t *)mask_dims, softmax_unscale);
   p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
   if (return_softmax) {
     FA_CHECK(softmax_ptr != nullptr, "return_softmax needs softmax_ptr");
@@ -192,11 +210,12 @@ bool flash_attn_varlen_fwd(
   p.softmax_lse = (float *)softmax_lse_ptr;
   p.cu_seqlens_q = cu_seqlens_q; p.cu_seqlens_k = cu_seqlens_k;
   p.varlen_padded_input = varlen_padded_input ? 1 : 0;
+  resolve_varlen_totals(p, stream);
   if (rng_state) {
     uint64_t st[2] = {seed, offset};
     FA_CUDA(cudaMemcpyAsync(rng_state, st, sizeof(st), cudaMemcpyHostToDevice, stream));
   }
-  (void)softmax_ptr; (void)softmax_unscale; (void)mask_dims;
+  (void)softmax_ptr;
   fa::run_fwd(p, stream);
   FA_END
 }
@@ -252,10 +271,12 @@ bool flash_attn_varlen_bwd(
     int dv_head_stride, int do_row_stride, int do_head_stride, int dq_batch_stride, int dk_batch_stride,
     int dv_batch_stride, int do_batch_stride, bool varlen_padded_input) {
   FA_BEGIN
-  unsupported(attn_mask != nullptr, "dense attn_mask");
   FA_CHECK(cu_seqlens_q && cu_seqlens_k, "cu_seqlens_q and cu_seqlens_k must be given");
   Params p = base_params(batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded, num_heads,
                          num_heads_k, head_size, head_size_rounded, softmax_scale, is_causal, is_bf16);
+  // mask rows are local to each sequence, its row stride is max_seqlen_k (flash_fwd_kernel.h:1104-1107 with the varlen
+  // params.seqlen_k = max_seqlen_k, csrc/capi/flash_attn.cu:730-733)
+  set_attn_mask(p, attn_mask, (const int64_t *)mask_dims, softmax_unscale);
   p.p_dropout = p_dropout; p.philox_seed = seed; p.philox_offset = offset;
   p.q = tensor(q, q_batch_stride, q_row_stride, q_head_stride);
   p.k = tensor(k, k_batch_stride, k_row_stride, k_head_stride);
@@ -270,9 +291,11 @@ bool flash_attn_varlen_bwd(
   p.dq_accum = (float *)dq_accum;
   p.cu_seqlens_q = cu_seqlens_q; p.cu_seqlens_k = cu_seqlens_k;
   p.varlen_padded_input = varlen_padded_input ? 1 : 0;
+  resolve_varlen_totals(p, stream);
+  p.dq_accum_batch_major = 1;               // the caller's dq_accum is (b, h, seqlen_q_rounded, d_rounded): flash_api.cpp:836-838
   p.dkv_expanded = 1;
   p.deterministic = (num_splits == 1);
-  (void)rng_state; (void)seed; (void)offset; (void)softmax_unscale; (void)mask_dims;
+  (void)rng_state; (void)seed; (void)offset;
   fa::run_bwd(p, stream);
   FA_END
 }

@@ -112,9 +112,9 @@ __device__ __forceinline__ bool bwd_decode(const Params &p, BwdTile &t) {
   t.m_lo = rlo / kB;
   t.m_hi = (max(rhi, 0) + kB - 1) / kB;
   if (t.m_hi < t.m_lo) t.m_hi = t.m_lo;
-  if (p.cu_seqlens_q && !p.varlen_padded_input) {
+  if (p.cu_seqlens_q && !p.varlen_padded_input && !p.dq_accum_batch_major) {
     t.acc_tile0 = (p.cu_seqlens_q[t.bi] + kB * t.bi) / kB;
-    t.acc_tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+    t.acc_tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b) / kB);
   } else {
     t.acc_tiles_per_head = p.seqlen_q_rounded / kB;
     t.acc_tile0 = t.bi * p.h * t.acc_tiles_per_head;  // batch-major: (b, h, tile)
@@ -764,8 +764,8 @@ __global__ void __launch_bounds__(256) bwd_convert_dq_kernel(const Params p) {
   const int row = idx / d8, c8 = idx % d8;
   if (row >= sq) return;
   int64_t tile;
-  if (p.cu_seqlens_q && !p.varlen_padded_input) {
-    const int tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+  if (p.cu_seqlens_q && !p.varlen_padded_input && !p.dq_accum_batch_major) {
+    const int tiles_per_head = (int)((p.total_q + (int64_t)kB * p.b) / kB);
     tile = (int64_t)hq * tiles_per_head + (p.cu_seqlens_q[bi] + kB * bi) / kB + row / kB;
   } else {
     const int tiles_per_head = p.seqlen_q_rounded / kB;
@@ -824,7 +824,7 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
   int64_t acc_tiles = 0;
   {
     int64_t tiles;
-    if (packed) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b + kB - 1) / kB);
+    if (packed && !p.dq_accum_batch_major) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b) / kB);
     else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
     acc_tiles = tiles;
     const int64_t acc_vec4 = tiles * (p.d_rounded / 32) * (kB * 32) / 4;
