@@ -120,6 +120,9 @@ typedef struct fa_b200_params {
   int32_t dq_accum_batch_major;   /* packed varlen backward: 1 = dq_accum is sized (b, h, seqlen_q_rounded, d_rounded) as
                                      the flat varlen symbol's callers allocate it (csrc/flash_attn/flash_api.cpp:836-838);
                                      0 = the compact h * floor((total_q + 128 * b) / 128) tiles */
+  const int32_t *seqused_q;       /* (b) int32 or NULL: only the first seqused_q[i] query rows of batch element i are
+                                     attended (csrc/flashmask_v2/seqlen.h:17-53); rows beyond are left untouched in out,
+                                     lse, dq.  Bottom-right alignment then uses seqused_q[i] as the query length. */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

@@ -18,8 +18,9 @@
  * Decode fields are honoured on run_mha_fwd: page_table (+ page_size, num_pages, page_table_batch_stride), kv_batch_idx
  * (+ b_k), leftpad_k, knew / vnew (appended at seqused_k, then attended), rotary_cos / rotary_sin (+ rotary_dim,
  * is_rotary_interleaved; applied to q and knew), softcap (forward and backward).
- * Fields accepted but requiring an unsupported feature make run_* throw: fp8 (is_e4m3), qv, seqused_q,
- * cu_seqlens_knew, p_dropout < 1, dv != d.
+ * seqused_q limits the query rows of each batch element (forward and backward).
+ * Fields accepted but requiring an unsupported feature make run_* throw: fp8 (is_e4m3), qv, cu_seqlens_knew,
+ * p_dropout < 1, dv != d.
  */
 #ifndef FA_B200_HANDLE_H_
 #define FA_B200_HANDLE_H_

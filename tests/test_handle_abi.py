@@ -290,3 +290,55 @@ def test_handle_paged_append_decode(fa, rotary):
     torch.testing.assert_close(pool_k.float(), kref.float(), atol=2e-2, rtol=8e-3)
     check_2x("out", o, ref, pt, atol=2e-3)
     hf.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("with_k", [False, True])
+def test_handle_seqused_q(fa, causal, with_k):
+    """seqused_q (+ seqused_k) on a padded batch (csrc/flashmask_v2/seqlen.h:17-91): element i attends its first
+    seqused_q[i] rows over its first seqused_k[i] keys, bottom-right aligned on those lengths; the rest stays untouched."""
+    from tests._util import check_2x, check_lse, oracle_all
+    lib = capi.load()
+    torch.manual_seed(0)
+    b, s, h, hk, d = 3, 512, 4, 2, 128
+    dev = "cuda"
+    q, g = [torch.randn(b, s, h, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    k, v = [torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    used_q, used_k = [512, 130, 77], ([512, 300, 77] if with_k else [s] * b)
+    uq = torch.tensor(used_q, device=dev, dtype=torch.int32)
+    uk = torch.tensor(used_k, device=dev, dtype=torch.int32)
+    sentinel = 7.0
+    o, dq = torch.full_like(q, sentinel), torch.full_like(q, sentinel)
+    dk, dv = torch.full_like(k, sentinel), torch.full_like(v, sentinel)
+    lse = torch.full((b, h, s), sentinel, device=dev, dtype=torch.float32)
+    stream = torch.cuda.current_stream().cuda_stream
+    common = dict(b=b, seqlen_q=s, seqlen_k=s, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d), is_bf16=True,
+                  is_causal=causal, num_splits=1, arch=100, num_sm=148, softmax_lse_ptr=lse, seqused_q=uq)
+    if with_k:
+        common.update(seqused_k=uk)
+    hf = Handle(lib, "fa3", "fwd")
+    _set_qkvo(hf, q, k, v, o)
+    hf.set(**common)
+    hf.call("run_mha_fwd", stream)
+    hb = Handle(lib, "fa3", "bwd")
+    _set_qkvo(hb, q, k, v, o)
+    hb.set(**common)
+    for name, t in (("do", g), ("dq", dq), ("dk", dk), ("dv", dv)):
+        hb.set(**{f"{name}_ptr": t, f"{name}_batch_stride": t.stride(0), f"{name}_row_stride": t.stride(1),
+                  f"{name}_head_stride": t.stride(2)})
+    hb.call("run_mha_bwd", stream)
+    torch.cuda.synchronize()
+    for i in range(b):
+        nq, nk = used_q[i], used_k[i]
+        mask = orc.causal_mask_bottom_right(nq, nk).to(dev) if causal else None
+        ref = oracle_all(q[i:i + 1, :nq], k[i:i + 1, :nk], v[i:i + 1, :nk], g[i:i + 1, :nq], mask, lse_empty=float("-inf"))
+        check_2x(f"out[{i}]", o[i:i + 1, :nq], *ref["out"])
+        check_lse(lse[i:i + 1, :, :nq], ref["lse"])
+        check_2x(f"dq[{i}]", dq[i:i + 1, :nq], *ref["dq"])
+        check_2x(f"dk[{i}]", dk[i:i + 1, :nk], *ref["dk"])
+        check_2x(f"dv[{i}]", dv[i:i + 1, :nk], *ref["dv"])
+        assert (o[i, nq:] == sentinel).all() and (dq[i, nq:] == sentinel).all() and (lse[i, :, nq:] == sentinel).all()
+        for t_ in (dk[i, nk:], dv[i, nk:]):            # keys beyond seqused_k receive no gradient: untouched or zero
+            assert ((t_ == sentinel) | (t_ == 0)).all()
+    hf.close(); hb.close()

@@ -54,7 +54,7 @@ class Params(C.Structure):
         ("leftpad_k", C.c_void_p), ("softcap", C.c_float),
         ("alibi_slopes", C.c_void_p), ("alibi_batch_stride", C.c_int64),
         ("attn_bias", C.c_void_p), ("bias_batch_mod", C.c_int32), ("bias_rows", C.c_int32), ("ds_out", C.c_void_p),
-        ("dq_accum_batch_major", C.c_int32),
+        ("dq_accum_batch_major", C.c_int32), ("seqused_q", C.c_void_p),
     ]
 
 

@@ -158,6 +158,7 @@ __device__ __forceinline__ void seq_bounds(const Params &p, int bi, int &q_row0,
     sk = p.seqlen_k; k_row0 = 0; k_batched = true;
   }
   if (p.seqused_k) sk = p.seqused_k[bi];
+  if (p.seqused_q) sq = min(sq, p.seqused_q[bi]);
 }
 
 // Element-level mask rule. TRUE = masked.

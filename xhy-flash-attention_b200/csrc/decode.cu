@@ -415,7 +415,7 @@ template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s
 bool decode_supported(const Params &p) {
   if (p.force_generic) return false;
   if (p.d != 64 && p.d != 128) return false;
-  if (p.cu_seqlens_q || p.cu_seqlens_k || p.lt_start) return false;
+  if (p.cu_seqlens_q || p.cu_seqlens_k || p.lt_start || p.seqused_q) return false;
   if (p.seqlen_q * (p.h / p.h_k) > kDMaxRows) return false;   // beyond that the tcgen05 forward is the better tool
   if (p.page_table && (p.page_size <= 0 || p.page_size % kDT != 0 || p.num_pages <= 0)) return false;
   const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);

@@ -56,7 +56,6 @@ Params common_params(const Flash_fwd_params &h) {
   require(!h.is_e4m3 && !h.is_fp32, "only fp16 / bf16 inputs are supported");
   require(h.softcap >= 0.f, "softcap must be >= 0");
   require(h.qv_ptr == nullptr, "qv is not supported");
-  require(h.seqused_q == nullptr, "seqused_q is not supported");
   require(h.cu_seqlens_knew == nullptr, "cu_seqlens_knew is not supported");
   require((h.knew_ptr == nullptr) == (h.vnew_ptr == nullptr), "knew_ptr and vnew_ptr go together");
   require((h.rotary_cos_ptr == nullptr) == (h.rotary_sin_ptr == nullptr), "rotary_cos_ptr and rotary_sin_ptr go together");
@@ -77,6 +76,7 @@ Params common_params(const Flash_fwd_params &h) {
   p.total_q = h.cu_seqlens_q ? h.total_q : -1;
   p.total_k = h.cu_seqlens_k ? h.total_k : -1;
   p.cu_seqlens_q = h.cu_seqlens_q; p.cu_seqlens_k = h.cu_seqlens_k; p.seqused_k = h.seqused_k;
+  p.seqused_q = h.seqused_q;
   p.softmax_scale = h.scale_softmax;
   p.lse_empty_is_neg_inf = 1;                          // csrc/flashmask_v2/softmax.h:153
   p.is_causal = h.is_causal ? 1 : 0;
