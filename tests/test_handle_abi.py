@@ -308,6 +308,9 @@ def test_handle_seqused_q(fa, causal, with_k):
     used_q, used_k = [512, 130, 77], ([512, 300, 77] if with_k else [s] * b)
     uq = torch.tensor(used_q, device=dev, dtype=torch.int32)
     uk = torch.tensor(used_k, device=dev, dtype=torch.int32)
+    for i in range(b):                               # a cache tail holds arbitrary bits: make them the worst ones
+        k[i, used_k[i]:] = float("nan")
+        v[i, used_k[i]:] = float("nan")
     sentinel = 7.0
     o, dq = torch.full_like(q, sentinel), torch.full_like(q, sentinel)
     dk, dv = torch.full_like(k, sentinel), torch.full_like(v, sentinel)
@@ -328,6 +331,7 @@ def test_handle_seqused_q(fa, causal, with_k):
         hb.set(**{f"{name}_ptr": t, f"{name}_batch_stride": t.stride(0), f"{name}_row_stride": t.stride(1),
                   f"{name}_head_stride": t.stride(2)})
     hb.call("run_mha_bwd", stream)
+    assert capi.last_kernel_kind() == 2              # tcgen05 kernels, with or without seqused_k
     torch.cuda.synchronize()
     for i in range(b):
         nq, nk = used_q[i], used_k[i]

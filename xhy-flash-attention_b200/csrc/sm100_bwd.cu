@@ -364,6 +364,20 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
         __syncwarp();
       };
       mbar_wait(bar(BB_KV_FULL), 0);
+      if (p.seqused_k != nullptr && t.n0 + kB > t.sk) {
+        // KV cache: rows at or beyond the used length hold arbitrary bits (possibly NaN).  Their P is masked to zero, but
+        // 0 * NaN would still reach dS (through dP = dO.V) and dQ (through dS.K): zero the tail rows of both tiles once.
+        // A row is 128 bytes in each 64-column box, whatever the swizzle (same as the forward's V tail).
+        const int first = max(t.sk - t.n0, 0);
+        for (int i = first * 8 + lane; i < kB * 8; i += 32)
+#pragma unroll
+          for (int hf = 0; hf < HD / 64; ++hf) {
+            sts128(sK + hf * kHalfBytes + i * 16, 0u, 0u, 0u, 0u);
+            sts128(sV + hf * kHalfBytes + i * 16, 0u, 0u, 0u, 0u);
+          }
+        fence_proxy_async_smem();
+        __syncwarp();
+      }
       mbar_wait(bar(BB_Q_FULL + 0), 0);
       tc_fence_after();
       kmajor_pair(TS_, sK, sbase + L::kQ, bar(BB_S_FULL));
@@ -873,7 +887,6 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
   if (!p.dq_accum) return no("no dq_accum workspace");
   if (p.d_rounded != round_up(p.d, 32) || p.seqlen_q_rounded % kB != 0 || p.seqlen_q_rounded < p.seqlen_q)
     return no("rounded sizes are not the documented ones");
-  if (p.seqused_k) return no("seqused_k");
   if (p.deterministic && p.lt_start) return no("deterministic + FlashMask (key blocks skip query blocks irregularly)");
   if (p.deterministic && p.p_dropout > 0.f) return no("deterministic + dropout");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f || p.deterministic)) return no("dense attn_mask with FlashMask / dropout / deterministic");
