@@ -42,8 +42,7 @@ for name, (b, s, h, hk, causal) in {"c3": (8, 8192, 32, 8, True), "c2": (8, 2048
             return torch.autograd.grad(o, (q, k, v), g)
         tf = timed(lambda: fwd())
         ts = timed(step)
-        with torch.no_grad():
-            outs[tag] = (fwd().float(), *[x.float() for x in step()])
+        outs[tag] = (fwd().detach().float(), *[x.float() for x in step()])
         row[tag] = {"fwd_ms": tf, "fwd_tflops": fl / tf / 1e9, "fwd_bwd_ms": ts, "fwd_bwd_tflops": 3.5 * fl / ts / 1e9}
     row["max_abs_diff_out_dq_dk_dv"] = [float((a - c).abs().max()) for a, c in zip(outs["ours"], outs["upstream"])]
     row["speedup_fwd_bwd"] = row["upstream"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"]
