@@ -3,7 +3,7 @@ ships in the image (FA2 mma.sync kernels recompiled for sm_100 -- the kind of ke
 in the same process, on the same tensors, alternating with this repo's kernels.  A comparator only: nothing in the
 product path imports it.
     python tools/yardstick_upstream.py [out.json]
-Prints one line per workload (C3, C2 fwd+bwd; C5b decode) and the max abs difference between the two outputs."""
+Prints one line per workload (C3, C2 fwd+bwd; C5b decode; C4 varlen fwd+bwd) and the max abs difference between the two outputs."""
 import importlib, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -69,5 +69,30 @@ row["max_abs_diff_out"] = float((outs["ours"] - outs["upstream"]).abs().max())
 row["speedup"] = row["upstream"]["ms"] / row["ours"]["ms"]
 res["workloads"]["c5b_decode"] = row
 print("c5b", json.dumps(row), flush=True)
+del q, kc, vc, outs
+torch.cuda.empty_cache()
+
+# C4 varlen: 64 sequences (128..16k tokens, 262144 in total), cu_seqlens encoding, causal (lengths from bench.c4_lengths)
+from bench import c4_lengths
+lens_l = c4_lengths()
+total, h, hk = sum(lens_l), 32, 8
+fl = 3.5 * 4.0 * h * 128 * sum(n * (n + 1) // 2 for n in lens_l)
+q = torch.randn(total, h, 128, device=dev, dtype=dt, requires_grad=True)
+k = torch.randn(total, hk, 128, device=dev, dtype=dt, requires_grad=True)
+v = torch.randn(total, hk, 128, device=dev, dtype=dt, requires_grad=True)
+g = torch.randn_like(q)
+cu = torch.tensor([0] + list(torch.tensor(lens_l).cumsum(0)), device=dev, dtype=torch.int32)
+row, outs = {}, {}
+for tag, mod in (("ours", ours), ("upstream", up), ("ours_again", ours)):
+    def step():
+        o = mod.flash_attn_varlen_func(q, k, v, cu, cu, max(lens_l), max(lens_l), 0.0, None, True)
+        return (o.detach(), *torch.autograd.grad(o, (q, k, v), g))
+    t = timed(step, warm=3, reps=5)
+    outs[tag] = [x.float() for x in step()]
+    row[tag] = {"fwd_bwd_ms": t, "fwd_bwd_tflops": fl / t / 1e9}
+row["max_abs_diff_out_dq_dk_dv"] = [float((a - c).abs().max()) for a, c in zip(outs["ours"], outs["upstream"])]
+row["speedup_fwd_bwd"] = row["upstream"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"]
+res["workloads"]["c4_varlen"] = row
+print("c4", json.dumps(row), flush=True)
 if len(sys.argv) > 1:
     json.dump(res, open(sys.argv[1], "w"), indent=1)
