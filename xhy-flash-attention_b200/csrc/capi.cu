@@ -13,10 +13,6 @@ namespace {
 
 using fa::Params;
 
-void unsupported(bool cond, const char *what) {
-  if (cond) throw fa::Error(std::string(what) + " is not supported by libflashattn_b200 (SURVEY.md 8(f))");
-}
-
 Params base_params(int batch_size, int seqlen_q, int seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded,
                    int num_heads, int num_heads_k, int head_size, int head_size_rounded, float softmax_scale,
                    bool is_causal, bool is_bf16) {
@@ -307,13 +303,14 @@ bool calc_reduced_attn_scores(
     int o_row_stride, int q_head_stride, int k_head_stride, int o_head_stride, int q_batch_stride,
     int k_batch_stride, int o_batch_stride) {
   FA_BEGIN
-  unsupported(return_softmax, "return_softmax");
   FA_CHECK(q && k && softmax_lse && reduced_scores, "calc_reduced_attn_scores: null tensor");
+  FA_CHECK(!return_softmax || softmax_ptr != nullptr, "calc_reduced_attn_scores: return_softmax needs softmax_ptr");
   FA_CHECK(head_size % 8 == 0 && head_size <= 256 && num_heads % num_heads_k == 0, "unsupported head configuration");
-  fa::reduced_scores(q, k, (const float *)softmax_lse, (float *)reduced_scores, batch_size, seqlen_q, seqlen_k,
-                     num_heads, num_heads_k, head_size, softmax_scale, is_bf16, q_batch_stride, q_row_stride,
-                     q_head_stride, k_batch_stride, k_row_stride, k_head_stride, stream);
-  (void)softmax_ptr; (void)num_splits; (void)o_row_stride; (void)o_head_stride; (void)o_batch_stride;
+  fa::reduced_scores(q, k, (const float *)softmax_lse, (float *)reduced_scores,
+                     return_softmax ? (float *)softmax_ptr : nullptr, batch_size, seqlen_q, seqlen_k, num_heads,
+                     num_heads_k, head_size, softmax_scale, is_bf16, q_batch_stride, q_row_stride, q_head_stride,
+                     k_batch_stride, k_row_stride, k_head_stride, stream);
+  (void)num_splits; (void)o_row_stride; (void)o_head_stride; (void)o_batch_stride;
   FA_END
 }
 

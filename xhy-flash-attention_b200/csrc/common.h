@@ -49,9 +49,9 @@ void run_splitkv(const Params &p, cudaStream_t s);
 void generic_fwd(const Params &p, cudaStream_t s);
 void generic_bwd(const Params &p, cudaStream_t s);
 void generic_splitkv_fwd(const Params &p, cudaStream_t s);
-void reduced_scores(const void *q, const void *k, const float *lse, float *out, int b, int sq, int sk, int h, int h_k,
-                    int d, float scale, int is_bf16, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs, int64_t krs,
-                    int64_t khs, cudaStream_t s);
+void reduced_scores(const void *q, const void *k, const float *lse, float *out, float *probs, int b, int sq, int sk, int h,
+                    int h_k, int d, float scale, int is_bf16, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs,
+                    int64_t krs, int64_t khs, cudaStream_t s);
 // tcgen05 / TMA / TMEM kernels (sm_100a): return false when the shape is outside their envelope.
 bool sm100_fwd_supported(const Params &p, std::string *why);
 void sm100_fwd(const Params &p, cudaStream_t s);

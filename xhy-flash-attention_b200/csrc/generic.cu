@@ -421,11 +421,13 @@ __global__ void __launch_bounds__(kWarps * 32) generic_dkv_kernel(const Params p
   }
 }
 
-// reduced[b, h, k] = sum_q exp(scale * q.k - lse[q])   (csrc/flash_attn/src/calc_reduced_attn_scores_kernel.h:93-110)
+// reduced[b, h, k] += sum_q exp(scale * q.k - lse[q])   (csrc/flash_attn/src/calc_reduced_attn_scores_kernel.h:93-110;
+// the reference ADDS into the caller's buffer with atomicAdd, :111-116, so does this -- one writer per element here).
+// probs != NULL (return_softmax): the fp32 probabilities themselves, (b, h, sq, sk) row-major (ibid.:56-90,262-278).
 template <typename T>
 __global__ void __launch_bounds__(kWarps * 32)
-reduced_scores_kernel(const T *q, const T *k, const float *lse, float *out, int sq, int sk, int h, int h_k, int d,
-                      float scale, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs, int64_t krs, int64_t khs) {
+reduced_scores_kernel(const T *q, const T *k, const float *lse, float *out, float *probs, int sq, int sk, int h, int h_k,
+                      int d, float scale, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs, int64_t krs, int64_t khs) {
   __shared__ float k_s[kWarps][kMaxD];
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int hq = blockIdx.y, bi = blockIdx.z;
@@ -436,15 +438,20 @@ reduced_scores_kernel(const T *q, const T *k, const float *lse, float *out, int 
   for (int e = lane; e < d; e += 32) k_s[warp][e] = to_f(krow[e]);
   __syncwarp();
   const float *l = lse + ((int64_t)bi * h + hq) * sq;
+  float *prow = probs ? probs + ((int64_t)bi * h + hq) * sq * (int64_t)sk + col : nullptr;
   float acc = 0.f;
   for (int i = lane; i < sq; i += 32) {
     const float li = l[i];
-    if (isinf(li)) continue;
-    const float s = dot_row(k_s[warp], q + bi * qbs + (int64_t)i * qrs + hq * qhs, d) * scale;
-    acc += __expf(s - li);
+    float pv = 0.f;
+    if (!isinf(li)) {
+      const float s = dot_row(k_s[warp], q + bi * qbs + (int64_t)i * qrs + hq * qhs, d) * scale;
+      pv = __expf(s - li);
+    }
+    acc += pv;
+    if (prow) prow[(int64_t)i * sk] = pv;
   }
   acc = warp_sum(acc);
-  if (lane == 0) out[((int64_t)bi * h + hq) * sk + col] = acc;
+  if (lane == 0) out[((int64_t)bi * h + hq) * sk + col] += acc;
 }
 
 }  // namespace
@@ -486,17 +493,17 @@ void generic_bwd(const Params &p, cudaStream_t s) {
   note_launch(1); note_launch(1); note_launch(1);
 }
 
-void reduced_scores(const void *q, const void *k, const float *lse, float *out, int b, int sq, int sk, int h, int h_k,
-                    int d, float scale, int is_bf16, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs, int64_t krs,
-                    int64_t khs, cudaStream_t s) {
+void reduced_scores(const void *q, const void *k, const float *lse, float *out, float *probs, int b, int sq, int sk, int h,
+                    int h_k, int d, float scale, int is_bf16, int64_t qbs, int64_t qrs, int64_t qhs, int64_t kbs,
+                    int64_t krs, int64_t khs, cudaStream_t s) {
   dim3 grid(ceil_div(sk, kWarps), h, b);
   if (is_bf16)
     reduced_scores_kernel<__nv_bfloat16><<<grid, kWarps * 32, 0, s>>>((const __nv_bfloat16 *)q, (const __nv_bfloat16 *)k,
-                                                                     lse, out, sq, sk, h, h_k, d, scale, qbs, qrs, qhs,
-                                                                     kbs, krs, khs);
+                                                                     lse, out, probs, sq, sk, h, h_k, d, scale, qbs,
+                                                                     qrs, qhs, kbs, krs, khs);
   else
-    reduced_scores_kernel<__half><<<grid, kWarps * 32, 0, s>>>((const __half *)q, (const __half *)k, lse, out, sq, sk,
-                                                              h, h_k, d, scale, qbs, qrs, qhs, kbs, krs, khs);
+    reduced_scores_kernel<__half><<<grid, kWarps * 32, 0, s>>>((const __half *)q, (const __half *)k, lse, out, probs, sq,
+                                                              sk, h, h_k, d, scale, qbs, qrs, qhs, kbs, krs, khs);
   FA_CUDA(cudaGetLastError());
   note_launch(1);
 }
