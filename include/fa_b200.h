@@ -196,6 +196,12 @@ int fa_b200_abi_version(void);
 int fa_b200_last_kernel_kind(void);
 /* number of kernels launched by this library (all threads) since the last reset */
 int64_t fa_b200_launch_count(int reset);
+/* Why the last fa_b200_fwd / fa_b200_bwd / flash_attn_* call of this thread left the tcgen05 kernels for the generic
+ * SIMT family ("" if it did not, or if the caller asked for it with force_generic).  The same text is printed to
+ * stderr once per distinct reason unless the environment variable FA_B200_QUIET is set: a drop-in must not get two
+ * orders of magnitude slower without saying so.  fa_b200_fallback_count: such calls, process-wide. */
+const char *fa_b200_last_fallback_reason(void);
+int64_t fa_b200_fallback_count(int reset);
 
 #ifdef __cplusplus
 }

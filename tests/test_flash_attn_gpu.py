@@ -37,15 +37,51 @@ def _run_and_check(fa, q, k, v, g, causal, generic, mask=None, **kw):
     check_2x("dv", dv, *ref["dv"])
 
 
-@pytest.mark.parametrize("generic", [False, True], ids=["tc", "generic"])
+# the reference's grids: head dims tests/test_flash_attn.py:336,527; (seqlen_q, seqlen_k) :531; seqlen :341
+REF_HEAD_DIMS = [32, 40, 59, 64, 80, 96, 111, 128, 160, 192, 224, 256]
+REF_SEQ_PAIRS = [(113, 203), (128, 217), (113, 211), (108, 256), (256, 512), (512, 256), (1024, 1024), (1023, 1024),
+                 (1024, 1023), (2048, 2048)]
+REF_SEQLENS = [97, 128, 200, 256, 257, 384, 512, 768, 1024, 1025, 2048]
+
+
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("d", [32, 59, 64, 96, 128, 160])
-@pytest.mark.parametrize("sq,sk", [(113, 203), (128, 217), (256, 512), (108, 256), (1023, 1024), (512, 256), (384, 384)])
-def test_flash_attn_output(fa, sq, sk, d, causal, dtype, generic):
-    # shapes from the reference list (tests/test_flash_attn.py:531); gqa with 6 q-heads, 2 kv-heads
+@pytest.mark.parametrize("d", REF_HEAD_DIMS)
+@pytest.mark.parametrize("sq,sk", REF_SEQ_PAIRS + [(384, 384)])
+def test_flash_attn_output(fa, capi, sq, sk, d, causal, dtype):
+    # the reference's whole (shape, head dim) grid; gqa with 6 q-heads, 2 kv-heads
     q, k, v, g = _inputs(2, sq, sk, 6, 2, d, dtype)
-    _run_and_check(fa, q, k, v, g, causal, generic)
+    _run_and_check(fa, q, k, v, g, causal, False)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [32, 59, 64, 96, 128, 160, 256])
+@pytest.mark.parametrize("sq,sk", [(113, 203), (128, 217), (256, 512), (108, 256), (1023, 1024), (512, 256), (384, 384)])
+def test_flash_attn_output_generic(fa, sq, sk, d, causal, dtype):
+    # the SIMT family as an independent second CUDA implementation
+    q, k, v, g = _inputs(2, sq, sk, 6, 2, d, dtype)
+    _run_and_check(fa, q, k, v, g, causal, True)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", REF_HEAD_DIMS)
+@pytest.mark.parametrize("seqlen", REF_SEQLENS)
+def test_flash_attn_qkvpacked_grid(fa, seqlen, d, causal):
+    # tests/test_flash_attn.py:333-347 (dropout_p = 0 half; the dropout half lives in tests/test_dropout_gpu.py)
+    torch.manual_seed(0)
+    b, h = 4 if seqlen < 2048 else 2, 4
+    qkv = torch.randn(b, seqlen, 3, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, seqlen, h, d, device=DEV, dtype=torch.bfloat16)
+    out, lse, _ = fa.flash_attn_qkvpacked_func(qkv, 0.0, None, causal, True)
+    (dqkv,) = torch.autograd.grad(out, qkv, g)
+    mask = orc.causal_mask_top_left(seqlen, seqlen).to(DEV) if causal else None
+    q, k, v = qkv.detach().unbind(2)
+    ref = oracle_all(q, k, v, g, mask)
+    check_2x("out", out, *ref["out"])
+    check_lse(lse, ref["lse"])
+    for i, n in enumerate(("dq", "dk", "dv")):
+        check_2x(n, dqkv[:, :, i], *ref[n])
 
 
 @pytest.mark.parametrize("mha_type", ["mha", "mqa", "gqa"])

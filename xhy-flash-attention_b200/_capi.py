@@ -95,6 +95,9 @@ def load() -> C.CDLL:
     lib.fa_b200_last_kernel_kind.restype = C.c_int
     lib.fa_b200_launch_count.argtypes = [C.c_int]
     lib.fa_b200_launch_count.restype = C.c_int64
+    lib.fa_b200_last_fallback_reason.restype = C.c_char_p
+    lib.fa_b200_fallback_count.argtypes = [C.c_int]
+    lib.fa_b200_fallback_count.restype = C.c_int64
     lib.fa_b200_profile_enable.argtypes = [C.c_int]
     lib.fa_b200_profile_enable.restype = None
     lib.fa_b200_profile_last_ms.argtypes = [C.c_int]
@@ -159,3 +162,12 @@ def launch_count(reset: bool = False) -> int:
 
 def last_kernel_kind() -> int:
     return int(load().fa_b200_last_kernel_kind())
+
+
+def last_fallback_reason() -> str:
+    """Why the last call of this thread ran on the generic SIMT kernels ("" if it ran on tcgen05)."""
+    return load().fa_b200_last_fallback_reason().decode("utf-8", "replace")
+
+
+def fallback_count(reset: bool = False) -> int:
+    return int(load().fa_b200_fallback_count(1 if reset else 0))

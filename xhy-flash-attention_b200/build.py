@@ -60,7 +60,8 @@ def build(verbose: bool = False, force: bool = False) -> str:
         for old in glob.glob(os.path.join(OBJ_DIR, "*.o")):
             os.remove(old)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
-    headers = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h")))
+    headers = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) +
+                     glob.glob(os.path.join(ROOT, "include", "*.h")))
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         results = list(ex.map(lambda s: _compile(s, headers, verbose), srcs))
     objs = [r[0] for r in results]

@@ -3,10 +3,13 @@
 // Error convention follows the reference (csrc/capi/flash_attn.cu:45-67): every body is wrapped in
 // try/catch, the message is kept in thread-local storage and the call returns false.
 // There is no CPU path here: every entry point enqueues CUDA kernels on the caller's stream.
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <atomic>
 #include <mutex>
+#include <vector>
 
 #include "common.h"
 #include "../../include/fa_capi.h"
@@ -22,16 +25,39 @@ void note_launch(int kind) {
   g_launches.fetch_add(1, std::memory_order_relaxed);
 }
 
-static bool tls_profile = false;
-static cudaEvent_t tls_events[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
-static bool tls_marked[2] = {false, false};
+// Optional per-kernel timing (fa_b200_profile_*).  Process-wide on purpose: a backward launched from autograd's worker
+// thread is read back from the thread that enabled profiling.  One mutex serialises the few host-side touches.
+static std::atomic<bool> g_profile{false};
+static std::mutex g_profile_mu;
+static cudaEvent_t g_events[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+static bool g_marked[2] = {false, false};
 
 void profile_mark(int slot, bool begin, cudaStream_t s) {
-  if (!tls_profile) return;
-  cudaEvent_t &e = tls_events[slot][begin ? 0 : 1];
+  if (!g_profile.load(std::memory_order_relaxed)) return;
+  std::lock_guard<std::mutex> lk(g_profile_mu);
+  cudaEvent_t &e = g_events[slot][begin ? 0 : 1];
   if (!e) FA_CUDA(cudaEventCreate(&e));
   FA_CUDA(cudaEventRecord(e, s));
-  if (!begin) tls_marked[slot] = true;
+  if (!begin) g_marked[slot] = true;
+}
+
+// A call that leaves the tcgen05 envelope runs on the generic SIMT kernels, two to three orders of magnitude slower.
+// That must not be silent: the reason is kept per thread (fa_b200_last_fallback_reason), counted process-wide
+// (fa_b200_fallback_count) and printed to stderr once per distinct reason unless FA_B200_QUIET is set.
+static thread_local std::string tls_fallback_reason;
+static std::atomic<int64_t> g_fallbacks{0};
+static void note_fallback(const char *pass, const std::string &why) {
+  tls_fallback_reason = std::string(pass) + ": " + why;
+  g_fallbacks.fetch_add(1, std::memory_order_relaxed);
+  static std::mutex mu;
+  static std::vector<std::string> seen;
+  static const bool quiet = getenv("FA_B200_QUIET") != nullptr;
+  if (quiet) return;
+  std::lock_guard<std::mutex> lk(mu);
+  for (const auto &x : seen) if (x == tls_fallback_reason) return;
+  seen.push_back(tls_fallback_reason);
+  fprintf(stderr, "[libflashattn_b200] %s -> generic SIMT kernels (slow path; this message is printed once per reason)\n",
+          tls_fallback_reason.c_str());
 }
 
 struct DevInfo { int sm_count; int cc_major; int cc_minor; };
@@ -83,11 +109,17 @@ void run_fwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   // return_softmax needs the element-wise generic pass; so do softcap / ALiBi and the KV-cache addressing modes outside
   // the decode kernel (inference features).  Dropout, the dense attn_mask and softcap have tcgen05 instantiations.
-  const bool special = p.s_dmask != nullptr ||
-                       p.alibi_slopes != nullptr || p.page_table != nullptr || p.kv_batch_idx != nullptr ||
-                       p.leftpad_k != nullptr || p.attn_bias != nullptr;
-  if (!p.force_generic && !special && sm100_fwd_supported(p, &why)) sm100_fwd(p, s);
-  else generic_fwd(p, s);
+  const char *special = p.s_dmask != nullptr ? "return_softmax (S_dmask)"
+                        : p.alibi_slopes != nullptr ? "alibi_slopes outside the decode kernel"
+                        : p.page_table != nullptr ? "paged KV outside the decode kernel"
+                        : p.kv_batch_idx != nullptr ? "kv_batch_idx outside the decode kernel"
+                        : p.leftpad_k != nullptr ? "leftpad_k outside the decode kernel"
+                        : p.attn_bias != nullptr ? "attn_bias (FA1 bias path)" : nullptr;
+  if (p.force_generic) { generic_fwd(p, s); return; }      // asked for by the caller (tests, FA1 symbols): not a fallback
+  if (special) why = special;
+  if (!special && sm100_fwd_supported(p, &why)) { tls_fallback_reason.clear(); sm100_fwd(p, s); return; }
+  note_fallback("forward", why);
+  generic_fwd(p, s);
 }
 
 void run_bwd(const Params &p, cudaStream_t s) {
@@ -97,9 +129,13 @@ void run_bwd(const Params &p, cudaStream_t s) {
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
-  const bool special = p.alibi_slopes != nullptr || p.attn_bias != nullptr || p.ds_out != nullptr;   // dropout / dense mask / softcap: own instantiations
-  if (!p.force_generic && !special && sm100_bwd_supported(p, &why)) sm100_bwd(p, s);
-  else generic_bwd(p, s);
+  const char *special = p.alibi_slopes != nullptr ? "alibi_slopes"
+                        : (p.attn_bias != nullptr || p.ds_out != nullptr) ? "attn_bias / dbias (FA1 bias path)" : nullptr;
+  if (p.force_generic) { generic_bwd(p, s); return; }
+  if (special) why = special;
+  if (!special && sm100_bwd_supported(p, &why)) { tls_fallback_reason.clear(); sm100_bwd(p, s); return; }
+  note_fallback("backward", why);
+  generic_bwd(p, s);
 }
 
 void run_splitkv(const Params &p, cudaStream_t s) {
@@ -137,15 +173,24 @@ void flash_attn_set_error(const char *msg) {
 
 const char *flash_attn_error(void) { return fa::tls_error ? fa::tls_error.get() : ""; }
 
-void fa_b200_profile_enable(int on) { fa::tls_profile = on != 0; fa::tls_marked[0] = fa::tls_marked[1] = false; }
+void fa_b200_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(fa::g_profile_mu);
+  fa::g_profile.store(on != 0);
+  fa::g_marked[0] = fa::g_marked[1] = false;
+}
+
+// why the last fa_b200_fwd / fa_b200_bwd / flash_attn_* call of this thread left the tcgen05 kernels ("" if it did not)
+const char *fa_b200_last_fallback_reason(void) { return fa::tls_fallback_reason.c_str(); }
+int64_t fa_b200_fallback_count(int reset) { return reset ? fa::g_fallbacks.exchange(0) : fa::g_fallbacks.load(); }
 
 // elapsed device time (ms) of the last forward kernel (slot 0) / backward main kernel (slot 1) launched on this
 // thread while profiling was enabled; -1 if none.  Blocks until that kernel has finished.
 float fa_b200_profile_last_ms(int slot) {
-  if (slot < 0 || slot > 1 || !fa::tls_marked[slot]) return -1.f;
+  std::lock_guard<std::mutex> lk(fa::g_profile_mu);
+  if (slot < 0 || slot > 1 || !fa::g_marked[slot]) return -1.f;
   float ms = -1.f;
-  if (cudaEventSynchronize(fa::tls_events[slot][1]) != cudaSuccess) return -1.f;
-  if (cudaEventElapsedTime(&ms, fa::tls_events[slot][0], fa::tls_events[slot][1]) != cudaSuccess) return -1.f;
+  if (cudaEventSynchronize(fa::g_events[slot][1]) != cudaSuccess) return -1.f;
+  if (cudaEventElapsedTime(&ms, fa::g_events[slot][0], fa::g_events[slot][1]) != cudaSuccess) return -1.f;
   return ms;
 }
 
