@@ -185,6 +185,15 @@ bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse
                        int64_t lse_row_stride, int64_t lse_head_stride,
                        int64_t lse_step_row_stride, int64_t lse_step_head_stride, cudaStream_t stream);
 
+/* The same merge over a batch in ONE launch: o / o_step rows of batch element i start at i * batch stride (elements;
+ * rows inside a batch element are contiguous (rows, h, d)), lse / lse_step index = i * batch stride + row * row stride +
+ * head * head stride.  Lets ring attention merge into the second half of its running (b, s, h, d) output in place. */
+bool fa_b200_lse_merge_batched(void *o, float *lse, const void *o_step, const float *lse_step, int batch, int64_t rows,
+                               int heads, int head_size, int is_bf16, int o_is_fp32, int64_t o_batch_stride,
+                               int64_t o_step_batch_stride, int64_t lse_batch_stride, int64_t lse_row_stride,
+                               int64_t lse_head_stride, int64_t lse_step_batch_stride, int64_t lse_step_row_stride,
+                               int64_t lse_step_head_stride, cudaStream_t stream);
+
 /* Per-kernel device timing for bench.py's roofline (CUDA events recorded on the launch stream around the
  * dominant kernels).  slot 0 = forward kernel, slot 1 = backward main kernel.  Process-wide; not for concurrent use. */
 void fa_b200_profile_enable(int on);

@@ -265,3 +265,44 @@ def test_backward_deterministic(fa, case):
     for a, b_ in zip(runs[0], ref):
         torch.testing.assert_close(a.float(), b_.float(), atol=2e-2, rtol=2e-2)
     assert torch.equal(runs[0][1], ref[1]) and torch.equal(runs[0][2], ref[2])   # dk, dv never depended on the order
+
+
+@pytest.mark.parametrize("packed", [False, True])
+@pytest.mark.parametrize("causal", [False, True])
+def test_backward_expanded_head_grid(fa, causal, packed, monkeypatch):
+    """The shallow-grid mode of the backward (one CTA per (key block, q-head), dK/dV summed over the GQA group
+    afterwards) must give what the grouped mode gives; forced on here, chosen by the wave model in production."""
+    iface = importlib.import_module("xhy-flash-attention_b200.flash_attn_interface")
+    torch.manual_seed(0)
+    b, sq, sk, h, hk, d = 2, 300, 520, 8, 2, 128
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    kv = torch.randn(b, sk, 2, hk, d, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    g = torch.randn(b, sq, h, d, device=DEV, dtype=torch.bfloat16)
+    res = {}
+    for mode in (False, True):
+        monkeypatch.setattr(iface, "_FORCE_EXPANDED_HEADS", mode)
+        if packed:      # dk/dv are strided slices of one packed gradient
+            out = fa.flash_attn_kvpacked_func(q, kv, 0.0, None, causal)
+            dq, dkv = torch.autograd.grad(out, (q, kv), g)
+            res[mode] = (dq, dkv[:, :, 0], dkv[:, :, 1])
+        else:
+            k, v = kv[:, :, 0], kv[:, :, 1]
+            out = fa.flash_attn_func(q, k, v, 0.0, None, causal)
+            dq, dkv = torch.autograd.grad(out, (q, kv), g)
+            res[mode] = (dq, dkv[:, :, 0], dkv[:, :, 1])
+    mask = orc.causal_mask_top_left(sq, sk).to(DEV) if causal else None
+    ref = oracle_all(q.detach(), kv.detach()[:, :, 0], kv.detach()[:, :, 1], g, mask)
+    for i, n in enumerate(("dq", "dk", "dv")):
+        check_2x(n, res[True][i], *ref[n], atol=2e-4)
+        torch.testing.assert_close(res[True][i].float(), res[False][i].float(), atol=3e-2, rtol=3e-2)
+
+
+def test_prefer_expanded_heads_wave_model():
+    iface = importlib.import_module("xhy-flash-attention_b200.flash_attn_interface")
+    dev = torch.device("cuda", 0)
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    if sms != 148:
+        pytest.skip("wave model numbers below are for 148 SMs")
+    assert iface._prefer_expanded_heads(1, 8192, 32, 8, dev)        # 512 CTAs = 3.46 waves -> 2048 CTAs = 13.8 waves
+    assert not iface._prefer_expanded_heads(8, 8192, 32, 8, dev)    # BASELINE config 3: 4096 CTAs, deep enough
+    assert not iface._prefer_expanded_heads(2, 512, 8, 2, dev)      # under one wave

@@ -19,7 +19,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, causal, ret):
+def _worker(rank, world, port, causal, b, ret):
     try:
         from oracle import attention_oracle as orc
         from tests._util import check_2x, check_lse
@@ -31,10 +31,11 @@ def _worker(rank, world, port, causal, ret):
         os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         if ndev >= world:
             dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+            assert dist.get_backend() == "nccl"       # >= 2 GPUs visible: the K/V blocks must travel over NCCL
         else:
             dist.init_process_group("gloo", rank=rank, world_size=world)
         torch.manual_seed(0)
-        b, s, h, hk, d = 1, 1024 * world, 8, 2, 128
+        s, h, hk, d = 1024 * world, 8, 2, 128
         q = torch.randn(b, s, h, d, device=dev, dtype=torch.bfloat16)
         k = torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16)
         v = torch.randn(b, s, hk, d, device=dev, dtype=torch.bfloat16)
@@ -66,10 +67,12 @@ def _worker(rank, world, port, causal, ret):
             dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("b", [1, 2])
 @pytest.mark.parametrize("causal", [True, False])
-def test_ring_attention_two_ranks(fa, causal):
+def test_ring_attention_two_ranks(fa, causal, b):
+    # b = 2: the causal "second half" steps merge into strided views of the running output (one batched launch)
     world = 2
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), causal, ret), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), causal, b, ret), nprocs=world, join=True)
     assert dict(ret) == {r: "ok" for r in range(world)}, "\n".join(f"[{r}] {m}" for r, m in dict(ret).items())

@@ -91,6 +91,9 @@ def load() -> C.CDLL:
     lib.fa_b200_lse_merge.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int,
                                                          C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p])
     lib.fa_b200_lse_merge.restype = C.c_bool
+    lib.fa_b200_lse_merge_batched.argtypes = ([C.c_void_p] * 4 + [C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int] +
+                                              [C.c_int64] * 8 + [C.c_void_p])
+    lib.fa_b200_lse_merge_batched.restype = C.c_bool
     lib.fa_b200_abi_version.restype = C.c_int
     lib.fa_b200_last_kernel_kind.restype = C.c_int
     lib.fa_b200_launch_count.argtypes = [C.c_int]

@@ -324,8 +324,21 @@ bool fa_b200_lse_merge(void *o, float *lse, const void *o_step, const float *lse
                        int64_t lse_step_row_stride, int64_t lse_step_head_stride, cudaStream_t stream) {
   FA_BEGIN
   FA_CHECK(o && lse && o_step && lse_step, "lse_merge: null tensor");
-  fa::lse_merge(o, lse, o_step, lse_step, rows, heads, head_size, is_bf16, o_is_fp32, lse_row_stride,
-                lse_head_stride, lse_step_row_stride, lse_step_head_stride, stream);
+  fa::lse_merge(o, lse, o_step, lse_step, 1, rows, heads, head_size, is_bf16, o_is_fp32, lse_row_stride,
+                lse_head_stride, lse_step_row_stride, lse_step_head_stride, 0, 0, 0, 0, stream);
+  FA_END
+}
+
+bool fa_b200_lse_merge_batched(void *o, float *lse, const void *o_step, const float *lse_step, int batch, int64_t rows,
+                               int heads, int head_size, int is_bf16, int o_is_fp32, int64_t o_batch_stride,
+                               int64_t o_step_batch_stride, int64_t lse_batch_stride, int64_t lse_row_stride,
+                               int64_t lse_head_stride, int64_t lse_step_batch_stride, int64_t lse_step_row_stride,
+                               int64_t lse_step_head_stride, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(o && lse && o_step && lse_step, "lse_merge: null tensor");
+  fa::lse_merge(o, lse, o_step, lse_step, batch, rows, heads, head_size, is_bf16, o_is_fp32, lse_row_stride,
+                lse_head_stride, lse_step_row_stride, lse_step_head_stride, o_batch_stride, o_step_batch_stride,
+                lse_batch_stride, lse_step_batch_stride, stream);
   FA_END
 }
 

@@ -220,14 +220,15 @@ rotary_kernel(const T *x, T *out, const T *cosp, const T *sinp, const int32_t *o
 template <typename TO, typename TS>
 __global__ void __launch_bounds__(128)
 lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int64_t rows, int heads, int d,
-                 int64_t lrs, int64_t lhs, int64_t srs, int64_t shs) {
+                 int64_t lrs, int64_t lhs, int64_t srs, int64_t shs, int64_t obs, int64_t sbs, int64_t lbs, int64_t slbs) {
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int64_t item = (int64_t)blockIdx.x * 4 + warp;
   if (item >= rows * heads) return;
+  const int bi = blockIdx.y;
   const int hh = item % heads;
   const int64_t row = item / heads;
-  const int64_t li = row * lrs + hh * lhs;
-  const float l1 = lse[li], l2 = lse_step[row * srs + hh * shs];
+  const int64_t li = bi * lbs + row * lrs + hh * lhs;
+  const float l1 = lse[li], l2 = lse_step[bi * slbs + row * srs + hh * shs];
   const bool e1 = isinf(l1), e2 = isinf(l2);
   if (e2) return;  // nothing to add
   float w1, w2, ln;
@@ -238,9 +239,24 @@ lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int
     ln = mx + __logf(s);
     w1 = __expf(l1 - ln); w2 = __expf(l2 - ln);
   }
-  TO *po = o + item * d;
-  const TS *ps = o_step + item * d;
-  for (int e = lane; e < d; e += 32) po[e] = from_f<TO>(w1 * to_f(po[e]) + w2 * to_f(ps[e]));
+  TO *po = o + bi * obs + item * d;
+  const TS *ps = o_step + bi * sbs + item * d;
+  if (d % 4 == 0) {         // 4 elements per lane and step: 16-byte (fp32) / 8-byte (16-bit) accesses
+    for (int e = lane * 4; e < d; e += 128) {
+      float a[4], b[4];
+      if constexpr (sizeof(TO) == 4) { const float4 t = *reinterpret_cast<const float4 *>(po + e); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+      else { const uint2 t = *reinterpret_cast<const uint2 *>(po + e); const TO *te = reinterpret_cast<const TO *>(&t);
+             for (int i = 0; i < 4; ++i) a[i] = to_f(te[i]); }
+      { const uint2 t = *reinterpret_cast<const uint2 *>(ps + e); const TS *te = reinterpret_cast<const TS *>(&t);
+        for (int i = 0; i < 4; ++i) b[i] = to_f(te[i]); }
+      for (int i = 0; i < 4; ++i) a[i] = w1 * a[i] + w2 * b[i];
+      if constexpr (sizeof(TO) == 4) *reinterpret_cast<float4 *>(po + e) = make_float4(a[0], a[1], a[2], a[3]);
+      else { uint2 t; TO *te = reinterpret_cast<TO *>(&t); for (int i = 0; i < 4; ++i) te[i] = from_f<TO>(a[i]);
+             *reinterpret_cast<uint2 *>(po + e) = t; }
+    }
+  } else {
+    for (int e = lane; e < d; e += 32) po[e] = from_f<TO>(w1 * to_f(po[e]) + w2 * to_f(ps[e]));
+  }
   __syncwarp();
   if (lane == 0) lse[li] = ln;
 }
@@ -341,16 +357,16 @@ void rotary(const void *x, void *out, const void *cosp, const void *sinp, const 
   note_launch(1);
 }
 
-void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
-               int is_bf16, int o_is_fp32, int64_t lrs, int64_t lhs, int64_t srs, int64_t shs, cudaStream_t s) {
-  dim3 grid((unsigned)((rows * heads + 3) / 4));
-  if (o_is_fp32) {
-    if (is_bf16) lse_merge_kernel<float, __nv_bfloat16><<<grid, 128, 0, s>>>((float *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
-    else lse_merge_kernel<float, __half><<<grid, 128, 0, s>>>((float *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
-  } else {
-    if (is_bf16) lse_merge_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 128, 0, s>>>((__nv_bfloat16 *)o, lse, (const __nv_bfloat16 *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
-    else lse_merge_kernel<__half, __half><<<grid, 128, 0, s>>>((__half *)o, lse, (const __half *)o_step, lse_step, rows, heads, d, lrs, lhs, srs, shs);
-  }
+void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int batch, int64_t rows, int heads, int d,
+               int is_bf16, int o_is_fp32, int64_t lrs, int64_t lhs, int64_t srs, int64_t shs, int64_t obs, int64_t sbs,
+               int64_t lbs, int64_t slbs, cudaStream_t s) {
+  if (batch <= 0 || rows <= 0) return;
+  dim3 grid((unsigned)((rows * heads + 3) / 4), (unsigned)batch);
+#define FA_MERGE(TO, TS) lse_merge_kernel<TO, TS><<<grid, 128, 0, s>>>((TO *)o, lse, (const TS *)o_step, lse_step, rows, \
+                                                                      heads, d, lrs, lhs, srs, shs, obs, sbs, lbs, slbs)
+  if (o_is_fp32) { if (is_bf16) FA_MERGE(float, __nv_bfloat16); else FA_MERGE(float, __half); }
+  else { if (is_bf16) FA_MERGE(__nv_bfloat16, __nv_bfloat16); else FA_MERGE(__half, __half); }
+#undef FA_MERGE
   FA_CUDA(cudaGetLastError());
   note_launch(1);
 }

@@ -81,9 +81,10 @@ void append_kv_paged(const Params &p, const void *k_new, const void *v_new, int 
 void rotary(const void *x, void *out, const void *cosp, const void *sinp, const int32_t *offsets, int batch, int seqlen,
             int heads, int d, int rdim, int seqlen_ro, int interleaved, int fixed, int is_bf16, int64_t xbs, int64_t xrs,
             int64_t xhs, int64_t obs, int64_t ors, int64_t ohs, cudaStream_t s);
-void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int64_t rows, int heads, int d,
+void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, int batch, int64_t rows, int heads, int d,
                int is_bf16, int o_is_fp32, int64_t lse_row_stride, int64_t lse_head_stride, int64_t step_row_stride,
-               int64_t step_head_stride, cudaStream_t s);
+               int64_t step_head_stride, int64_t o_batch_stride, int64_t o_step_batch_stride, int64_t lse_batch_stride,
+               int64_t lse_step_batch_stride, cudaStream_t s);
 
 // ---- device helpers shared by every kernel ------------------------------------------------------
 struct SeqInfo {

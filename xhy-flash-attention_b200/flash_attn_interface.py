@@ -89,6 +89,27 @@ def _fill_mask(p: Params, mask: _Mask, b: int, sk: int, keep: list):
         p.flashmask_maxmin = ws.data_ptr()
 
 
+_SM_COUNT = {}
+_FORCE_EXPANDED_HEADS = None      # tests: True / False overrides the wave model below
+
+
+def _prefer_expanded_heads(b, sk, h, h_k, device) -> bool:
+    """Wave model of the backward grid: CTAs = key blocks x heads x batch, one CTA per SM.  True when the per-q-head
+    grid loses at least 6 points less to the last, partly filled wave than the per-kv-head grid (small grids only)."""
+    if _FORCE_EXPANDED_HEADS is not None:
+        return _FORCE_EXPANDED_HEADS
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _SM_COUNT:
+        _SM_COUNT[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    sms = _SM_COUNT[idx]
+    nkb = (sk + 127) // 128
+    grouped = nkb * h_k * b
+    if grouped < sms or grouped >= 8 * sms:      # under one wave nothing is lost; deep grids amortise the last wave
+        return False
+    eff = lambda n: (n / sms) / -(-n // sms)
+    return eff(nkb * h * b) > eff(grouped) + 0.06
+
+
 def _new_rng_state():
     """(seed, offset) for the Philox dropout mask, drawn from torch's CPU generator (reproducible under
     ``torch.manual_seed``); kept as a small CPU tensor so that saving it for backward costs no device sync.  The
@@ -185,6 +206,16 @@ def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p,
     # slack per sequence so tile-granular reduce-adds never cross sequences)
     acc_rows = h * round_up(total_q + 128 * b, 128) if varlen else b * h * sq_r
     dq_accum = torch.empty(acc_rows * d_r, dtype=torch.float32, device=q.device)
+    # GQA: one CTA normally owns (key block, kv-head) and walks the q-heads of the group, so dK/dV need no reduction.
+    # When that grid is only a few waves deep and the last wave is mostly empty (ring steps, batch 1 per GPU: 512 CTAs
+    # = 3.46 waves on 148 SMs), one CTA per (key block, Q-head) fills the machine better; the per-q-head dK/dV are then
+    # summed over the group afterwards -- the reference's only mode (csrc/flash_attn/flash_api.cpp:628-635,682-686).
+    dk_out, dv_out = dk, dv
+    expand = h != h_k and d <= 128 and _prefer_expanded_heads(b, sk, h, h_k, q.device)
+    if expand:
+        dk = torch.empty(k.shape[:-2] + (h, d), dtype=k.dtype, device=k.device)
+        dv = torch.empty_like(dk)
+        p.dkv_expanded = 1
     p.q, p.k, p.v, p.o, p.dout, p.dq, p.dk, p.dv = [tdesc(t, packed=varlen) for t in (q, k, v, out, dout, dq, dk, dv)]
     p.softmax_lse, p.softmax_d, p.dq_accum = softmax_lse.data_ptr(), softmax_d.data_ptr(), dq_accum.data_ptr()
     # no dk/dv accumulator: the kernels reduce a GQA group inside one CTA (TMEM), p.dkv_accum stays NULL
@@ -201,7 +232,13 @@ def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, dropout_p,
         p.philox_seed, p.philox_offset = int(rng_state[0]), int(rng_state[1])
     with torch.cuda.device(q.device):
         _capi.check(_capi.load().fa_b200_bwd(p, _capi.stream_ptr(q.device)), "fa_b200_bwd")
-    return dq, dk, dv, softmax_d
+    if expand:
+        g = h // h_k
+        torch.sum(dk.view(dk.shape[:-2] + (h_k, g, d)), dim=-2, out=dk_out) if dk_out.is_contiguous() else \
+            dk_out.copy_(dk.view(dk.shape[:-2] + (h_k, g, d)).sum(dim=-2))
+        torch.sum(dv.view(dv.shape[:-2] + (h_k, g, d)), dim=-2, out=dv_out) if dv_out.is_contiguous() else \
+            dv_out.copy_(dv.view(dv.shape[:-2] + (h_k, g, d)).sum(dim=-2))
+    return dq, dk_out, dv_out, softmax_d
 
 
 def _flash_attn_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,

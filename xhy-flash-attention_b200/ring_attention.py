@@ -79,25 +79,31 @@ def _cuda_block_bwd(dout, q, k, v, out, lse, softmax_scale, causal):
 
 
 def _cuda_merge(o_acc, lse_acc, o_step, lse_step):
-    """(o_acc fp32 (b, s, h, d), lse_acc fp32 (b, s, h)) <- merge with (o_step 16-bit (b, s, h, d), lse_step (b, h, s))."""
+    """(o_acc fp32 (b, s, h, d), lse_acc fp32 (b, s, h)) <- merge with (o_step 16-bit (b, s, h, d), lse_step (b, h, s)).
+    One launch for the whole batch; ``o_acc`` / ``lse_acc`` may be views along the sequence (the second half of the
+    running output): only their batch stride differs from a contiguous tensor's."""
     lib = _capi.load()
     b, s, h, d = o_acc.shape
-    assert o_acc.is_contiguous() and lse_acc.is_contiguous() and o_step.is_contiguous() and lse_step.is_contiguous()
+    assert o_acc.stride()[1:] == (h * d, d, 1) and lse_acc.stride()[1:] == (h, 1)
+    assert o_step.stride()[1:] == (h * d, d, 1) and lse_step.stride()[1:] == (s, 1)
     is_bf16 = 1 if o_step.dtype == torch.bfloat16 else 0
-    stream = _capi.stream_ptr(o_acc.device)
     with torch.cuda.device(o_acc.device):
-        for i in range(b):
-            _capi.check(lib.fa_b200_lse_merge(o_acc[i].data_ptr(), lse_acc[i].data_ptr(), o_step[i].data_ptr(),
-                                              lse_step[i].data_ptr(), s, h, d, is_bf16, 1, h, 1, 1, s, stream),
-                        "fa_b200_lse_merge")
+        _capi.check(lib.fa_b200_lse_merge_batched(
+            o_acc.data_ptr(), lse_acc.data_ptr(), o_step.data_ptr(), lse_step.data_ptr(), b, s, h, d, is_bf16, 1,
+            o_acc.stride(0), o_step.stride(0), lse_acc.stride(0), h, 1, lse_step.stride(0), 1, s,
+            _capi.stream_ptr(o_acc.device)), "fa_b200_lse_merge_batched")
 
 
 class RingOps:
     """The three device operations the ring schedule is built from."""
 
     def __init__(self, block_fwd: Callable = _cuda_block_fwd, block_bwd: Callable = _cuda_block_bwd,
-                 merge: Callable = _cuda_merge):
+                 merge: Callable = _cuda_merge, exchange: bool = True):
         self.block_fwd, self.block_bwd, self.merge = block_fwd, block_bwd, merge
+        # exchange=False replays the identical schedule (same block shapes, masks, merges) WITHOUT send/recv: every step
+        # attends the rank's own K/V.  Results are meaningless; the run time is the compute-only time that
+        # bench.py subtracts from the real step to report the exposed communication (BASELINE.md C5a).
+        self.exchange = exchange
 
 
 _CUDA_OPS = RingOps()
@@ -113,7 +119,10 @@ class _Rotation:
     caller's stream; ``wait()`` makes the caller's stream wait for the transfer.
     """
 
-    def __init__(self, group, tensors, comm_stream=None):
+    def __init__(self, group, tensors, comm_stream=None, exchange=True):
+        if not exchange:                      # compute-only replay (RingOps.exchange)
+            self.recv, self.reqs, self.staged, self.stream, self.keep = list(tensors), [], None, None, []
+            return
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         nxt = dist.get_global_rank(group, (rank + 1) % world) if group is not None else (rank + 1) % world
         prv = dist.get_global_rank(group, (rank - 1) % world) if group is not None else (rank - 1) % world
@@ -148,8 +157,8 @@ class _Rotation:
             return self.staged
         if self.stream is not None:
             torch.cuda.current_stream().wait_stream(self.stream)
-            for t in self.keep + self.recv:
-                t.record_stream(torch.cuda.current_stream())
+            for t in self.keep + self.recv:      # allocated on the compute stream, used by the comm stream
+                t.record_stream(self.stream)
         return self.recv
 
 
@@ -189,25 +198,14 @@ def ring_forward(q, k, v, softmax_scale, causal, group=None, ops: RingOps = _CUD
     comm = _comm_stream(q)
     k_cur, v_cur = k.contiguous(), v.contiguous()
     for t in range(world):
-        rot = _Rotation(group, [k_cur, v_cur], comm) if t + 1 < world else None
+        rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange) if t + 1 < world else None
         src = (rank - t) % world
         plan = _step_plan(causal, rank, src)
         if plan is not None:
             qp, kp, cz = plan
-            o_step, lse_step = ops.block_fwd(_part(q, qp).contiguous(), _part(k_cur, kp).contiguous(),
-                                             _part(v_cur, kp).contiguous(), softmax_scale, cz)
-            if qp == "all":
-                ops.merge(o_acc, lse_acc, o_step.contiguous(), lse_step.contiguous())
-            else:  # only the second half of the local queries took part
-                half = s // 2
-                o_view, l_view = o_acc[:, half:], lse_acc[:, half:]
-                if o_view.is_contiguous() and l_view.is_contiguous():      # batch 1: merge in place, no copies
-                    ops.merge(o_view, l_view, o_step.contiguous(), lse_step.contiguous())
-                else:
-                    o_half, l_half = o_view.contiguous(), l_view.contiguous()
-                    ops.merge(o_half, l_half, o_step.contiguous(), lse_step.contiguous())
-                    o_view.copy_(o_half)
-                    l_view.copy_(l_half)
+            # halves are strided views (batch stride of the whole shard): the kernels take them as they are
+            o_step, lse_step = ops.block_fwd(_part(q, qp), _part(k_cur, kp), _part(v_cur, kp), softmax_scale, cz)
+            ops.merge(_part(o_acc, qp), _part(lse_acc, qp), o_step, lse_step)
         if rot is not None:
             k_cur, v_cur = rot.wait()
     return o_acc.to(q.dtype), lse_acc.transpose(1, 2).contiguous()
@@ -226,16 +224,15 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, causal, group=None, op
     acc_rot = None
     half = q.shape[1] // 2
     for t in range(world):
-        kv_rot = _Rotation(group, [k_cur, v_cur], comm) if t + 1 < world else None
+        kv_rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange) if t + 1 < world else None
         src = (rank - t) % world
         plan = _step_plan(causal, rank, src)
         dk_blk = dv_blk = None
         if plan is not None:
             qp, kp, cz = plan
-            lse_p = _part(lse, qp, dim=2).contiguous()
-            dq_p, dk_p, dv_p = ops.block_bwd(_part(dout, qp).contiguous(), _part(q, qp).contiguous(),
-                                             _part(k_cur, kp).contiguous(), _part(v_cur, kp).contiguous(),
-                                             _part(out, qp).contiguous(), lse_p, softmax_scale, cz)
+            lse_p = _part(lse, qp, dim=2).contiguous()      # (b, h, rows): the kernels index it densely
+            dq_p, dk_p, dv_p = ops.block_bwd(_part(dout, qp), _part(q, qp), _part(k_cur, kp), _part(v_cur, kp),
+                                             _part(out, qp), lse_p, softmax_scale, cz)
             _part(dq, qp).add_(dq_p)
             dk_blk, dv_blk = (kp, dk_p), (kp, dv_p)
         if acc_rot is not None:                      # accumulators of this block, as left by the previous rank
@@ -243,7 +240,7 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, causal, group=None, op
         if dk_blk is not None:
             _part(dk_acc, dk_blk[0]).add_(dk_blk[1])
             _part(dv_acc, dv_blk[0]).add_(dv_blk[1])
-        acc_rot = _Rotation(group, [dk_acc, dv_acc], comm)   # travels with the block; after `world` hops it is home
+        acc_rot = _Rotation(group, [dk_acc, dv_acc], comm, ops.exchange)   # travels with the block; after `world` hops it is home
         if kv_rot is not None:
             k_cur, v_cur = kv_rot.wait()
     dk_acc, dv_acc = acc_rot.wait()
