@@ -54,9 +54,12 @@ def flat_fwd(lib, q, k, v, causal, scale=None, fm=None, attn_mask=None, err=None
     (qr, qh, qb), (kr, kh, kb), (vr, vh, vb), (or_, oh, ob) = _strides(q), _strides(k), _strides(v), _strides(out)
     fm_args, keep = flashmask_args(fm, b, sk, q.device)
     mask_dims = _i64(list(attn_mask.shape)) if attn_mask is not None else None
+    # the reference's forward kernel stores (seed, offset) into rng_state UNCONDITIONALLY (flash_fwd_kernel.h:320-324),
+    # dropout or not: a caller must always pass two uint64 of device memory
+    rng_state = torch.zeros(2, dtype=torch.int64, device=q.device)
     lib.flash_attn_fwd.restype = C.c_bool
     ok = lib.flash_attn_fwd(
-        _vp(q), _vp(k), _vp(v), None, _vp(out), None, _vp(lse), C.c_int(b), C.c_int(sq), C.c_int(sk),
+        _vp(q), _vp(k), _vp(v), _vp(rng_state), _vp(out), None, _vp(lse), C.c_int(b), C.c_int(sq), C.c_int(sk),
         C.c_int(round_up(sq, 128)), C.c_int(round_up(sk, 128)), C.c_int(h), C.c_int(hk), C.c_int(d),
         C.c_int(round_up(d, 32)), C.c_float(0.0), C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal),
         C.c_bool(False), C.c_bool(q.dtype == torch.bfloat16), stream, C.c_uint64(0), C.c_uint64(0),
@@ -84,9 +87,10 @@ def flat_bwd(lib, g, q, k, v, out, lse, causal, scale=None, fm=None, num_splits=
     (qr, qh, qb), (kr, kh, kb), (vr, vh, vb), (or_, oh, ob) = _strides(q), _strides(k), _strides(v), _strides(out)
     (dqr, dqh, dqb), (dkr, dkh, dkb), (dvr, dvh, dvb), (gr, gh, gb) = _strides(dq), _strides(dk), _strides(dv), _strides(g)
     fm_args, keep = flashmask_args(fm, b, sk, q.device)
+    rng_state = torch.zeros(2, dtype=torch.int64, device=q.device)
     lib.flash_attn_bwd.restype = C.c_bool
     ok = lib.flash_attn_bwd(
-        _vp(g), _vp(q), _vp(k), _vp(v), _vp(out), _vp(softmax_d), _vp(lse), None, _vp(dq), _vp(dk), _vp(dv),
+        _vp(g), _vp(q), _vp(k), _vp(v), _vp(out), _vp(softmax_d), _vp(lse), _vp(rng_state), _vp(dq), _vp(dk), _vp(dv),
         _vp(dq_accum), C.c_int(b), C.c_int(sq), C.c_int(sk), C.c_int(sq_r), C.c_int(sk_r), C.c_int(h), C.c_int(hk),
         C.c_int(d), C.c_int(d_r), C.c_float(0.0), C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal),
         C.c_bool(q.dtype == torch.bfloat16), C.c_int(num_splits), stream, C.c_uint64(0), C.c_uint64(0), None, None,

@@ -52,6 +52,8 @@ def test_flash_attn_output(fa, capi, sq, sk, d, causal, dtype):
     # the reference's whole (shape, head dim) grid; gqa with 6 q-heads, 2 kv-heads
     q, k, v, g = _inputs(2, sq, sk, 6, 2, d, dtype)
     _run_and_check(fa, q, k, v, g, causal, False)
+    fa.flash_attn_func(q.detach(), k.detach(), v.detach(), 0.0, None, causal)
+    assert capi.last_kernel_kind() == 2, f"forward left the tcgen05 kernels: {capi.last_fallback_reason()}"
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])

@@ -55,6 +55,8 @@ void reduced_scores(const void *q, const void *k, const float *lse, float *out, 
 // tcgen05 / TMA / TMEM kernels (sm_100a): return false when the shape is outside their envelope.
 bool sm100_fwd_supported(const Params &p, std::string *why);
 void sm100_fwd(const Params &p, cudaStream_t s);
+bool sm100_fwd2_eligible(const Params &p);     // split-row forward (sm100_fwd2.cu): plain calls, head dims up to 256
+void sm100_fwd2(const Params &p, cudaStream_t s);
 bool sm100_bwd_supported(const Params &p, std::string *why);
 void sm100_bwd(const Params &p, cudaStream_t s);
 // bandwidth kernels

@@ -12,6 +12,7 @@
 //   The two Q tiles ping-pong on the tensor core: while one warpgroup runs softmax the MMA warp works for the other.
 //
 // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,256+HD) O1 [256+HD, 256+2HD).
+#include <cstdlib>
 #include <math_constants.h>
 #include <type_traits>
 
@@ -985,7 +986,7 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCa
 
 bool sm100_fwd_supported(const Params &p, std::string *why) {
   auto no = [&](const char *w) { if (why) *why = w; return false; };
-  if (p.d > 128) return no("head_size > 128");
+  if (p.d > 128 && !sm100_fwd2_eligible(p)) return no("head_size > 128 together with FlashMask / dropout / attn_mask / softcap");
   if (p.num_splits > 1) return no("split-KV");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f)) return no("dense attn_mask together with FlashMask / dropout");
   if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.attn_mask)) return no("softcap together with FlashMask / dropout / attn_mask");
@@ -1015,6 +1016,10 @@ template <int HD, bool kBf16> void dispatch_fwd(const Params &p, cudaStream_t s)
 }  // namespace
 
 void sm100_fwd(const Params &p, cudaStream_t s) {
+  // plain calls (and every head dim above 128) take the split-row kernel of sm100_fwd2.cu; FA_B200_FWD2=0 keeps the
+  // one-thread-per-row kernel for head dims <= 128 (A/B measurements)
+  static const bool use_fwd2 = [] { const char *e = getenv("FA_B200_FWD2"); return !(e && e[0] == '0'); }();
+  if (sm100_fwd2_eligible(p) && (p.d > 128 || use_fwd2)) { sm100_fwd2(p, s); return; }
   if (p.d <= 64) { if (p.is_bf16) dispatch_fwd<64, true>(p, s); else dispatch_fwd<64, false>(p, s); }
   else { if (p.is_bf16) dispatch_fwd<128, true>(p, s); else dispatch_fwd<128, false>(p, s); }
 }
