@@ -44,8 +44,11 @@ template <int HD> struct F2 {
   static constexpr int kStages = HD <= 128 ? 4 : (HD <= 192 ? 3 : 2);    // K/V ring depth (tiles of 128 x HD)
   static constexpr int kSmWarps = 8 * kQT;                               // softmax warps: two warpgroups per Q tile
   static constexpr int kThreads = (kSmWarps + 4) * 32;                   // + {issuer, producer, 2 idle}
-  static constexpr int kSmRegs = HD <= 128 ? 112 : 200;                  // register budget of a softmax thread
+  // setmaxnreg moves registers inside the CTA's OWN allocation (threads x registers at launch), not the SM's file:
+  // 640 threads launch with 96 -> 61440 = 512 x 104 + 128 x 64; 384 threads launch with 168 -> 64512 >= 256 x 200 + 128 x 96
+  static constexpr int kSmRegs = HD <= 128 ? 104 : 200;                  // register budget of a softmax thread
   static constexpr int kAuxRegs = HD <= 128 ? 64 : 96;                   // ... of an issuer / producer / idle thread
+  static_assert(kSmWarps * 32 * kSmRegs + 128 * kAuxRegs <= kThreads * (HD <= 128 ? 96 : 168), "register pool of the CTA");
   static constexpr int kTileBytes = kBM * HD * 2;
   static constexpr int kQOff = 0;
   static constexpr int kKVOff = kQT * kTileBytes;
@@ -198,7 +201,6 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
   constexpr uint32_t kBoxBytes = kBM * 128;    // one box: 128 rows x 128 bytes
 
   if (warp >= kSmWarps) {
-    // register pool at 640 threads (head dim <= 128): 512 softmax threads x 112 + 128 x 64 = 65536 exactly
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(L::kAuxRegs));
     if (warp == kSmWarps + 1) {
       // ======================= TMA producer =======================
