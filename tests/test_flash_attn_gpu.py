@@ -51,7 +51,11 @@ REF_SEQLENS = [97, 128, 200, 256, 257, 384, 512, 768, 1024, 1025, 2048]
 def test_flash_attn_output(fa, capi, sq, sk, d, causal, dtype):
     # the reference's whole (shape, head dim) grid; gqa with 6 q-heads, 2 kv-heads
     q, k, v, g = _inputs(2, sq, sk, 6, 2, d, dtype)
+    capi.fallback_count(reset=True)
     _run_and_check(fa, q, k, v, g, causal, False)
+    # every head dim of the reference's grid runs on the tcgen05 kernels, forward AND backward (the backward runs on
+    # autograd's thread: the process-wide fallback counter sees it)
+    assert capi.fallback_count() == 0, "a pass left the tcgen05 kernels"
     fa.flash_attn_func(q.detach(), k.detach(), v.detach(), 0.0, None, causal)
     assert capi.last_kernel_kind() == 2, f"forward left the tcgen05 kernels: {capi.last_fallback_reason()}"
 

@@ -32,7 +32,7 @@ for name, (b, s, h, hk, d, causal) in cases.items():
     for _ in range(7):
         fwd(); torch.cuda.synchronize(); ts.append(lib.fa_b200_profile_last_ms(0))
     tb = []
-    if d <= 128:
+    if True:
         for _ in range(3):
             o = fwd(); torch.autograd.grad(o, (q, k, v), g); torch.cuda.synchronize(); tb.append(lib.fa_b200_profile_last_ms(1))
     lib.fa_b200_profile_enable(0)

@@ -59,6 +59,10 @@ bool sm100_fwd2_eligible(const Params &p);     // split-row forward (sm100_fwd2.
 void sm100_fwd2(const Params &p, cudaStream_t s);
 bool sm100_bwd_supported(const Params &p, std::string *why);
 void sm100_bwd(const Params &p, cudaStream_t s);
+bool sm100_bwd_wide_eligible(const Params &p);   // head dims 129..256 (sm100_bwd_wide.cu): plain calls only
+void sm100_bwd_wide(const Params &p, cudaStream_t s);
+int64_t bwd_pre_dpsum(const Params &p, cudaStream_t s);        // shared pre / post passes of the backward (sm100_bwd.cu)
+void bwd_post_convert_dq(const Params &p, cudaStream_t s);
 // bandwidth kernels
 void splitkv_fwd(const Params &p, cudaStream_t s);
 void combine_fwd(const Params &p, cudaStream_t s);

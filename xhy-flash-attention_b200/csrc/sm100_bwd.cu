@@ -835,21 +835,7 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
   tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
   tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
   // 1. dPsum + zeroing of the fp32 dQ accumulator (one kernel)
-  int64_t acc_tiles = 0;
-  {
-    int64_t tiles;
-    if (packed && !p.dq_accum_batch_major) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b) / kB);
-    else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
-    acc_tiles = tiles;
-    const int64_t acc_vec4 = tiles * (p.d_rounded / 32) * (kB * 32) / 4;
-    dim3 grid(ceil_div(p.seqlen_q_rounded, 16), p.h, p.b);
-#ifdef FA_AB_MEMSET
-    FA_CUDA(cudaMemsetAsync(p.dq_accum, 0, (size_t)acc_vec4 * 16, s));
-#endif
-    bwd_dpsum_kernel<T><<<grid, 256, 0, s>>>(p, acc_vec4);
-    FA_CUDA(cudaGetLastError());
-    note_launch(2);
-  }
+  const int64_t acc_tiles = bwd_pre_dpsum(p, s);
   // 3. main kernel
   {
     if (kFM) flashmask_prepare(p, kB, s);   // per-128-key-block min/max of the mask vectors
@@ -871,19 +857,48 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
     note_launch(2);
   }
   // 4. dQ conversion
-  {
-    dim3 grid(ceil_div(p.seqlen_q * (p.d / 8), 256), p.h, p.b);
-    bwd_convert_dq_kernel<T, kBf16><<<grid, 256, 0, s>>>(p);
-    FA_CUDA(cudaGetLastError());
-    note_launch(2);
-  }
+  bwd_post_convert_dq(p, s);
+}
+
+template <typename T> void pre_dpsum_t(const Params &p, int64_t acc_vec4, cudaStream_t s) {
+  dim3 grid(ceil_div(p.seqlen_q_rounded, 16), p.h, p.b);
+  bwd_dpsum_kernel<T><<<grid, 256, 0, s>>>(p, acc_vec4);
+}
+template <typename T, bool kBf16> void post_convert_t(const Params &p, cudaStream_t s) {
+  dim3 grid(ceil_div(p.seqlen_q * (p.d / 8), 256), p.h, p.b);
+  bwd_convert_dq_kernel<T, kBf16><<<grid, 256, 0, s>>>(p);
 }
 
 }  // namespace
 
+// dPsum = rowsum(dO o O) and the zeroing of the tiled fp32 dQ accumulator, one launch; returns the number of 128-row
+// accumulator tiles.  Shared by the d <= 128 kernel above and the sliced kernel of sm100_bwd_wide.cu.
+int64_t bwd_pre_dpsum(const Params &p, cudaStream_t s) {
+  const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
+  int64_t tiles;
+  if (packed && !p.dq_accum_batch_major) tiles = (int64_t)p.h * ((p.total_q + (int64_t)kB * p.b) / kB);
+  else tiles = (int64_t)p.b * p.h * (p.seqlen_q_rounded / kB);
+  const int64_t acc_vec4 = tiles * (p.d_rounded / 32) * (kB * 32) / 4;
+#ifdef FA_AB_MEMSET
+  FA_CUDA(cudaMemsetAsync(p.dq_accum, 0, (size_t)acc_vec4 * 16, s));
+#endif
+  if (p.is_bf16) pre_dpsum_t<__nv_bfloat16>(p, acc_vec4, s); else pre_dpsum_t<__half>(p, acc_vec4, s);
+  FA_CUDA(cudaGetLastError());
+  note_launch(2);
+  return tiles;
+}
+
+// dQ = T(scale * dq_accum), un-tiling the accumulator
+void bwd_post_convert_dq(const Params &p, cudaStream_t s) {
+  if (p.is_bf16) post_convert_t<__nv_bfloat16, true>(p, s); else post_convert_t<__half, false>(p, s);
+  FA_CUDA(cudaGetLastError());
+  note_launch(2);
+}
+
 bool sm100_bwd_supported(const Params &p, std::string *why) {
   auto no = [&](const char *w) { if (why) *why = w; return false; };
-  if (p.d > 128) return no("head_size > 128");
+  if (p.d > 128 && !sm100_bwd_wide_eligible(p))
+    return no("head_size > 128 together with FlashMask / dropout / attn_mask / softcap / deterministic");
   if (!p.dq_accum) return no("no dq_accum workspace");
   if (p.d_rounded != round_up(p.d, 32) || p.seqlen_q_rounded % kB != 0 || p.seqlen_q_rounded < p.seqlen_q)
     return no("rounded sizes are not the documented ones");
@@ -903,6 +918,7 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
 }
 
 void sm100_bwd(const Params &p, cudaStream_t s) {
+  if (p.d > 128) { sm100_bwd_wide(p, s); return; }   // sliced kernel (sm100_bwd_wide.cu)
   const bool fm = p.lt_start != nullptr && p.flashmask_maxmin != nullptr;   // block skipping needs the workspace
   if (p.deterministic && !fm) {   // ordered dQ accumulation: its own instantiation, the default kernels carry none of it
     if (p.d <= 64) { if (p.is_bf16) launch_bwd<64, true, false, true>(p, s); else launch_bwd<64, false, false, true>(p, s); }

@@ -291,8 +291,7 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
     // dQ^T sits in TMEM with the slice's head-dim columns on the lanes: warp w holds columns 32w..32w+31 of the slice =
     // one 32-float chunk of dq_accum, 64 query rows deep.  Each lane writes its column into the staging rows (a row of
     // 32 floats per query, the accumulator's swizzle applied), 16 rows at a time, and lane 0 issues the bulk reduce-add.
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
-    const int w = warp - 8;
+    const int w = warp - 8;                                  // (keeps the 128 registers of the launch)
     const uint32_t lane_base = (uint32_t)(w * 32) << 16;
     const int chunk = t.slice * 4 + w;                       // 32-float chunk of the head dim
     const bool chunk_ok = chunk < p.d_rounded / 32;
