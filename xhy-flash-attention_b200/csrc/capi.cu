@@ -70,20 +70,11 @@ void set_flashmask(Params &p, const void *downstart, const int64_t *dims, const 
 }
 
 // The flat varlen symbols carry no total row counts, which the TMA descriptors of the tcgen05 kernels need as tensor
-// extents (the tail tile of the last sequence relies on the out-of-bounds zero fill).  Read cu_seqlens[b] back (8 bytes,
-// one stream synchronisation); while the stream is being captured into a CUDA graph that is not possible and the call
-// stays on the generic kernels.  Callers that know the totals use fa_b200_fwd / the handle ABI (total_q / total_k).
-void resolve_varlen_totals(Params &p, cudaStream_t stream) {
-  if (p.varlen_padded_input || p.total_q >= 0) return;
-  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-  FA_CUDA(cudaStreamIsCapturing(stream, &st));
-  if (st != cudaStreamCaptureStatusNone) return;
-  int32_t tq = -1, tk = -1;
-  FA_CUDA(cudaMemcpyAsync(&tq, p.cu_seqlens_q + p.b, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-  FA_CUDA(cudaMemcpyAsync(&tk, p.cu_seqlens_k + p.b, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-  FA_CUDA(cudaStreamSynchronize(stream));
-  p.total_q = tq; p.total_k = tk;
-}
+// extents (the tail tile of the last sequence relies on the out-of-bounds zero fill).  total_q / total_k stay -1 and
+// the launchers patch the row extent of their tensor maps ON THE DEVICE from cu_seqlens[b] (tma_host.cu:
+// patch_tma_rows): the call only enqueues work, as the reference's does (csrc/capi/flash_attn.cu:576-684), and stays on
+// the tcgen05 kernels under CUDA-graph capture.
+void resolve_varlen_totals(Params &, cudaStream_t) {}
 
 // shared argument translation of the two FA1 symbols (flash_attn_with_bias_mask.cu:301-350,433-491)
 Params fa1_params(int batch_size, int num_heads, int head_size, int max_seqlen_q_, int max_seqlen_k_, int total_q,

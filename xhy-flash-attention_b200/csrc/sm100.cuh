@@ -82,6 +82,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // ---------------------------------------------------------------- TMA
+// a tensor map that another kernel wrote to global memory (patch_tma_rows): make it visible to this thread's TMA unit
+__device__ __forceinline__ void tma_acquire_desc(const CUtensorMap *m) {
+  asm volatile("fence.proxy.tensormap::generic.acquire.gpu [%0], 128;" ::"l"(m) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
 }
@@ -228,5 +232,9 @@ struct TmaDesc4 {
 };
 // Encodes a 4-D tiled tensor map of 16-bit elements with 128-byte swizzle. Throws fa::Error on failure.
 CUtensorMap make_tma_4d(const TmaDesc4 &d);
+// Copies n (<= 4) host-encoded maps to a stream-ordered device allocation and patches dimension 2 (rows) of map i to
+// cu_seqlens_k[b] (k_like[i] != 0) or cu_seqlens_q[b] ON THE DEVICE (tma_host.cu).  cudaFreeAsync the result.
+CUtensorMap *patch_tma_rows(const CUtensorMap *maps, const int *k_like, int n, const int32_t *cu_q, const int32_t *cu_k,
+                            int b, cudaStream_t s);
 
 }  // namespace fa

@@ -235,8 +235,10 @@ template <bool kFM> struct MCursor {
 
 template <int HD, bool kBf16, bool kFM, bool kDet, bool kDrop, bool kMask, bool kCap>
 __global__ void __launch_bounds__(kBwdThreads, 1)
-bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, int *__restrict__ dq_sem) {
+bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_param, const BwdTma *__restrict__ tm_dev,
+           int *__restrict__ dq_sem) {
   using L = BwdSmem<HD>;
+  const BwdTma &tm = tm_dev ? *tm_dev : tm_param;   // device-patched maps (flat varlen symbols) or the launch's own
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t *smem = smem_raw;
@@ -270,6 +272,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm, 
   }
   if (warp == 12) tmem_alloc<512>(smem_u32(tmem_slot));
   if (warp == 13 && lane == 0) {
+    if (tm_dev) { tma_acquire_desc(&tm.q); tma_acquire_desc(&tm.k); tma_acquire_desc(&tm.v); tma_acquire_desc(&tm.dout); }
     tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v); tma_prefetch_desc(&tm.dout);
   }
   tc_fence_before();
@@ -829,11 +832,20 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
   using L = BwdSmem<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
-  BwdTma tm;
-  tm.q = make_tma_4d(bdesc(p.q, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b));
-  tm.dout = make_tma_4d(bdesc(p.dout, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b));
-  tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
-  tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b));
+  // packed tensors without host-known totals (the flat varlen symbols): the row extents are patched on the device
+  const bool dev_rows = packed && (p.total_q < 0 || p.total_k < 0);
+  const int64_t rows_q = packed ? (p.total_q >= 0 ? p.total_q : (int64_t)p.b * p.seqlen_q) : p.seqlen_q;
+  const int64_t rows_k = packed ? (p.total_k >= 0 ? p.total_k : (int64_t)p.b * p.seqlen_k) : p.seqlen_k;
+  BwdTma tm;   // member order q, k, v, dout
+  tm.q = make_tma_4d(bdesc(p.q, p.d, p.h, rows_q, packed ? 1 : p.b));
+  tm.dout = make_tma_4d(bdesc(p.dout, p.d, p.h, rows_q, packed ? 1 : p.b));
+  tm.k = make_tma_4d(bdesc(p.k, p.d, p.h_k, rows_k, packed ? 1 : p.b));
+  tm.v = make_tma_4d(bdesc(p.v, p.d, p.h_k, rows_k, packed ? 1 : p.b));
+  BwdTma *tm_dev = nullptr;
+  if (dev_rows) {
+    const int k_like[4] = {0, 1, 1, 0};
+    tm_dev = reinterpret_cast<BwdTma *>(patch_tma_rows(&tm.q, k_like, 4, p.cu_seqlens_q, p.cu_seqlens_k, p.b, s));
+  }
   // 1. dPsum + zeroing of the fp32 dQ accumulator (one kernel)
   const int64_t acc_tiles = bwd_pre_dpsum(p, s);
   // 3. main kernel
@@ -849,9 +861,10 @@ template <int HD, bool kBf16, bool kFM, bool kDet = false, bool kDrop = false, b
       FA_CUDA(cudaMemsetAsync(dq_sem, 0, sizeof(int) * (size_t)acc_tiles, s));
     }
     profile_mark(1, true, s);
-    kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm, dq_sem);
+    kern<<<grid, kBwdThreads, L::kDynBytes, s>>>(p, tm, tm_dev, dq_sem);
     profile_mark(1, false, s);
     const cudaError_t launch_err = cudaGetLastError();
+    if (tm_dev) cudaFreeAsync(tm_dev, s);
     if (dq_sem) FA_CUDA(cudaFreeAsync(dq_sem, s));
     FA_CUDA(launch_err);
     note_launch(2);
@@ -908,7 +921,8 @@ bool sm100_bwd_supported(const Params &p, std::string *why) {
   if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.deterministic || p.attn_mask)) return no("softcap with FlashMask / dropout / deterministic / attn_mask");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if ((p.cu_seqlens_q != nullptr) != (p.cu_seqlens_k != nullptr)) return no("need both cu_seqlens");
-  if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
+  if (packed && (p.total_q < 0 || p.total_k < 0) && !p.dq_accum_batch_major)
+    return no("varlen totals unknown and dq_accum not batch-major");   // the tiled accumulator is sized by total_q
   const int nb = packed ? 1 : p.b;
   if (!tma_ok_b(p.q, p.h, nb) || !tma_ok_b(p.dout, p.h, nb) || !tma_ok_b(p.k, p.h_k, nb) || !tma_ok_b(p.v, p.h_k, nb))
     return no("strides/alignment not TMA-compatible");

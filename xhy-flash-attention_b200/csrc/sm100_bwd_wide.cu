@@ -124,8 +124,9 @@ __device__ __forceinline__ int64_t wide_acc_tile(const Params &p, const WTile &t
 
 template <bool kBf16>
 __global__ void __launch_bounds__(kWThreads, 1)
-bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma tm) {
+bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma tm_param, const WTma *__restrict__ tm_dev) {
   using L = WSmem;
+  const WTma &tm = tm_dev ? *tm_dev : tm_param;   // device-patched maps (flat varlen symbols) or the launch's own
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t *smem = smem_raw;
@@ -154,6 +155,7 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
   }
   if (warp == 12) tmem_alloc<512>(smem_u32(tmem_slot));
   if (warp == 13 && lane == 0) {
+    if (tm_dev) { tma_acquire_desc(&tm.q); tma_acquire_desc(&tm.k); tma_acquire_desc(&tm.v); tma_acquire_desc(&tm.dout); }
     tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v); tma_prefetch_desc(&tm.dout);
   }
   tc_fence_before();
@@ -482,21 +484,31 @@ TmaDesc4 wdesc(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batc
 template <bool kBf16> void launch_wide(const Params &p, cudaStream_t s) {
   using L = WSmem;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
-  WTma tm;
+  const bool dev_rows = packed && (p.total_q < 0 || p.total_k < 0);
+  const int64_t rows_q = packed ? (p.total_q >= 0 ? p.total_q : (int64_t)p.b * p.seqlen_q) : p.seqlen_q;
+  const int64_t rows_k = packed ? (p.total_k >= 0 ? p.total_k : (int64_t)p.b * p.seqlen_k) : p.seqlen_k;
+  WTma tm;   // member order q, k, v, dout
   // columns at or beyond p.d are zero-filled by the TMA unit: the contraction always runs over 256
-  tm.q = make_tma_4d(wdesc(p.q, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b, kBQ));
-  tm.dout = make_tma_4d(wdesc(p.dout, p.d, p.h, packed ? p.total_q : p.seqlen_q, packed ? 1 : p.b, kBQ));
-  tm.k = make_tma_4d(wdesc(p.k, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b, kBK));
-  tm.v = make_tma_4d(wdesc(p.v, p.d, p.h_k, packed ? p.total_k : p.seqlen_k, packed ? 1 : p.b, kBK));
+  tm.q = make_tma_4d(wdesc(p.q, p.d, p.h, rows_q, packed ? 1 : p.b, kBQ));
+  tm.dout = make_tma_4d(wdesc(p.dout, p.d, p.h, rows_q, packed ? 1 : p.b, kBQ));
+  tm.k = make_tma_4d(wdesc(p.k, p.d, p.h_k, rows_k, packed ? 1 : p.b, kBK));
+  tm.v = make_tma_4d(wdesc(p.v, p.d, p.h_k, rows_k, packed ? 1 : p.b, kBK));
+  WTma *tm_dev = nullptr;
+  if (dev_rows) {
+    const int k_like[4] = {0, 1, 1, 0};
+    tm_dev = reinterpret_cast<WTma *>(patch_tma_rows(&tm.q, k_like, 4, p.cu_seqlens_q, p.cu_seqlens_k, p.b, s));
+  }
   bwd_pre_dpsum(p, s);
   auto kern = bwd_wide_kernel<kBf16>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kTotal, smem_set);
   dim3 grid(2 * ceil_div(p.seqlen_k, kBK), p.dkv_expanded ? p.h : p.h_k, p.b);
   profile_mark(1, true, s);
-  kern<<<grid, kWThreads, L::kTotal, s>>>(p, tm);
+  kern<<<grid, kWThreads, L::kTotal, s>>>(p, tm, tm_dev);
   profile_mark(1, false, s);
-  FA_CUDA(cudaGetLastError());
+  const cudaError_t launch_err = cudaGetLastError();
+  if (tm_dev) cudaFreeAsync(tm_dev, s);
+  FA_CUDA(launch_err);
   note_launch(2);
   bwd_post_convert_dq(p, s);
 }

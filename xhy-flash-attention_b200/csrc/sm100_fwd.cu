@@ -340,9 +340,10 @@ template <bool kDyn> struct TileWalk {
 
 template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask, bool kCap>
 __global__ void __launch_bounds__(kThreads, 1)
-fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, int num_m, int num_tiles,
-           int *__restrict__ tile_counter) {
+fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_param, const FwdTma *__restrict__ tm_dev,
+           int num_m, int num_tiles, int *__restrict__ tile_counter) {
   using L = FwdSmem<HD>;
+  const FwdTma &tm = tm_dev ? *tm_dev : tm_param;   // device-patched maps (flat varlen symbols) or the launch's own
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sbase = smem_u32(smem);
@@ -384,6 +385,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm, 
   }
   if (warp == 8) tmem_alloc<512>(smem_u32(tmem_slot));
   if (warp == 9 && lane == 0) {
+    if (tm_dev) { tma_acquire_desc(&tm.q); tma_acquire_desc(&tm.k); tma_acquire_desc(&tm.v); }
     tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v);
   }
   tc_fence_before();
@@ -955,12 +957,19 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCa
   using L = FwdSmem<HD>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
-  FA_CHECK(!packed_q || p.total_q >= 0, "varlen: total_q must be given");
-  FA_CHECK(!packed_k || p.total_k >= 0, "varlen: total_k must be given");
+  // packed tensors without host-known totals (the flat varlen symbols): the row extents are patched on the device
+  const bool dev_rows = (packed_q && p.total_q < 0) || (packed_k && p.total_k < 0);
+  const int64_t rows_q = packed_q ? (p.total_q >= 0 ? p.total_q : (int64_t)p.b * p.seqlen_q) : p.seqlen_q;
+  const int64_t rows_k = packed_k ? (p.total_k >= 0 ? p.total_k : (int64_t)p.b * p.seqlen_k) : p.seqlen_k;
   FwdTma tm;
-  tm.q = make_tma_4d(desc_for(p.q, p.d, p.h, packed_q ? p.total_q : p.seqlen_q, packed_q ? 1 : p.b, kBM));
-  tm.k = make_tma_4d(desc_for(p.k, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
-  tm.v = make_tma_4d(desc_for(p.v, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
+  tm.q = make_tma_4d(desc_for(p.q, p.d, p.h, rows_q, packed_q ? 1 : p.b, kBM));
+  tm.k = make_tma_4d(desc_for(p.k, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
+  tm.v = make_tma_4d(desc_for(p.v, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
+  FwdTma *tm_dev = nullptr;
+  if (dev_rows) {
+    const int k_like[3] = {0, 1, 1};
+    tm_dev = reinterpret_cast<FwdTma *>(patch_tma_rows(&tm.q, k_like, 3, p.cu_seqlens_q, p.cu_seqlens_k, p.b, s));
+  }
   const int num_m = ceil_div(p.seqlen_q, kBM * kTilesPerCta);
   const int num_tiles = p.b * p.h * num_m;
   if (kFM) flashmask_prepare(p, kBN, s, true);   // per-128-key-block min/max of the mask vectors
@@ -974,9 +983,10 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCa
     FA_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
   }
   profile_mark(0, true, s);
-  kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles, counter);
+  kern<<<grid, kThreads, L::kDynBytes, s>>>(p, tm, tm_dev, num_m, num_tiles, counter);
   profile_mark(0, false, s);
   const cudaError_t launch_err = cudaGetLastError();
+  if (tm_dev) cudaFreeAsync(tm_dev, s);
   if (counter) FA_CUDA(cudaFreeAsync(counter, s));
   FA_CUDA(launch_err);
   note_launch(2);
@@ -992,7 +1002,6 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
   if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.attn_mask)) return no("softcap together with FlashMask / dropout / attn_mask");
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   if (p.cu_seqlens_q && !p.cu_seqlens_k) return no("cu_seqlens_q without cu_seqlens_k");
-  if (packed && (p.total_q < 0 || p.total_k < 0)) return no("varlen totals unknown");
   if (p.cu_seqlens_k && !p.cu_seqlens_q) return no("cu_seqlens_k without cu_seqlens_q");
   if (!tma_ok(p.q, p.h, packed ? 1 : p.b) || !tma_ok(p.k, p.h_k, packed ? 1 : p.b) ||
       !tma_ok(p.v, p.h_k, packed ? 1 : p.b))

@@ -19,6 +19,7 @@
 // each half is produced by its own warpgroup.  Row maxima use the 3-input max (FMNMX3).
 //
 // TMEM columns: S slot 0 [0,128)  S slot 1 [128,256)  O0 [256,256+HD)  O1 [256+HD,256+2HD) (second O only for HD <= 128).
+#include <cstdlib>
 #include <math_constants.h>
 #include <type_traits>
 
@@ -39,16 +40,16 @@ struct Fwd2Tma {
   CUtensorMap q, k, v;
 };
 
-template <int HD> struct F2 {
-  static constexpr int kQT = HD <= 128 ? 2 : 1;                          // Q tiles per CTA
-  static constexpr int kStages = HD <= 128 ? 4 : (HD <= 192 ? 3 : 2);    // K/V ring depth (tiles of 128 x HD)
+template <int HD, int QT> struct F2 {
+  static constexpr int kQT = QT;                                         // Q tiles per CTA (2 needs 256 + 2 HD <= 512 TMEM columns)
+  static constexpr int kStages = HD <= 128 ? (QT == 2 ? 4 : 5) : (HD <= 192 ? 3 : 2);    // K/V ring depth (tiles of 128 x HD)
   static constexpr int kSmWarps = 8 * kQT;                               // softmax warps: two warpgroups per Q tile
   static constexpr int kThreads = (kSmWarps + 4) * 32;                   // + {issuer, producer, 2 idle}
   // setmaxnreg moves registers inside the CTA's OWN allocation (threads x registers at launch), not the SM's file:
   // 640 threads launch with 96 -> 61440 = 512 x 104 + 128 x 64; 384 threads launch with 168 -> 64512 >= 256 x 200 + 128 x 96
-  static constexpr int kSmRegs = HD <= 128 ? 104 : 200;                  // register budget of a softmax thread
-  static constexpr int kAuxRegs = HD <= 128 ? 64 : 96;                   // ... of an issuer / producer / idle thread
-  static_assert(kSmWarps * 32 * kSmRegs + 128 * kAuxRegs <= kThreads * (HD <= 128 ? 96 : 168), "register pool of the CTA");
+  static constexpr int kSmRegs = QT == 2 ? 104 : 200;                    // register budget of a softmax thread
+  static constexpr int kAuxRegs = QT == 2 ? 64 : 96;                     // ... of an issuer / producer / idle thread
+  static_assert(kSmWarps * 32 * kSmRegs + 128 * kAuxRegs <= kThreads * (QT == 2 ? 96 : 168), "register pool of the CTA");
   static constexpr int kTileBytes = kBM * HD * 2;
   static constexpr int kQOff = 0;
   static constexpr int kKVOff = kQT * kTileBytes;
@@ -158,10 +159,12 @@ __device__ __forceinline__ float exp2_poly(float x) {
   return __int_as_float(__float_as_int(q) + (__float_as_int(jm) << 23));
 }
 
-template <int HD, bool kBf16>
-__global__ void __launch_bounds__(F2<HD>::kThreads, 1)
-fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm, int num_m, int num_tiles) {
-  using L = F2<HD>;
+template <int HD, bool kBf16, int QT>
+__global__ void __launch_bounds__(F2<HD, QT>::kThreads, 1)
+fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm_param, const Fwd2Tma *__restrict__ tm_dev,
+            int num_m, int num_tiles) {
+  using L = F2<HD, QT>;
+  const Fwd2Tma &tm = tm_dev ? *tm_dev : tm_param;   // device-patched maps (flat varlen symbols) or the launch's own
   constexpr int kQT = L::kQT, kStages = L::kStages, kSmWarps = L::kSmWarps;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -190,6 +193,7 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
   }
   if (warp == kSmWarps) tmem_alloc<512>(smem_u32(tmem_slot));
   if (warp == kSmWarps + 1 && lane == 0) {
+    if (tm_dev) { tma_acquire_desc(&tm.q); tma_acquire_desc(&tm.k); tma_acquire_desc(&tm.v); }
     tma_prefetch_desc(&tm.q); tma_prefetch_desc(&tm.k); tma_prefetch_desc(&tm.v);
   }
   tc_fence_before();
@@ -615,27 +619,36 @@ TmaDesc4 desc2(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batc
   return x;
 }
 
-template <int HD, bool kBf16> void launch_fwd2(const Params &p, cudaStream_t s) {
-  using L = F2<HD>;
+template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1)> void launch_fwd2(const Params &p, cudaStream_t s) {
+  using L = F2<HD, QT>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
-  FA_CHECK(!packed_q || p.total_q >= 0, "varlen: total_q must be given");
-  FA_CHECK(!packed_k || p.total_k >= 0, "varlen: total_k must be given");
+  // packed tensors without host-known totals (the flat varlen symbols): the row extents are patched on the device
+  const bool dev_rows = (packed_q && p.total_q < 0) || (packed_k && p.total_k < 0);
+  const int64_t rows_q = packed_q ? (p.total_q >= 0 ? p.total_q : (int64_t)p.b * p.seqlen_q) : p.seqlen_q;
+  const int64_t rows_k = packed_k ? (p.total_k >= 0 ? p.total_k : (int64_t)p.b * p.seqlen_k) : p.seqlen_k;
   Fwd2Tma tm;
   // columns at or beyond p.d (head dims that are not a multiple of 64) are zero-filled by the TMA unit
-  tm.q = make_tma_4d(desc2(p.q, p.d, p.h, packed_q ? p.total_q : p.seqlen_q, packed_q ? 1 : p.b, kBM));
-  tm.k = make_tma_4d(desc2(p.k, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
-  tm.v = make_tma_4d(desc2(p.v, p.d, p.h_k, packed_k ? p.total_k : p.seqlen_k, packed_k ? 1 : p.b, kBN));
+  tm.q = make_tma_4d(desc2(p.q, p.d, p.h, rows_q, packed_q ? 1 : p.b, kBM));
+  tm.k = make_tma_4d(desc2(p.k, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
+  tm.v = make_tma_4d(desc2(p.v, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
+  Fwd2Tma *tm_dev = nullptr;
+  if (dev_rows) {
+    const int k_like[3] = {0, 1, 1};
+    tm_dev = reinterpret_cast<Fwd2Tma *>(patch_tma_rows(&tm.q, k_like, 3, p.cu_seqlens_q, p.cu_seqlens_k, p.b, s));
+  }
   const int num_m = ceil_div(p.seqlen_q, kBM * L::kQT);
   const int num_tiles = p.b * p.h * num_m;
-  auto kern = fwd2_kernel<HD, kBf16>;
+  auto kern = fwd2_kernel<HD, kBf16, QT>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
   profile_mark(0, true, s);
-  kern<<<grid, L::kThreads, L::kDynBytes, s>>>(p, tm, num_m, num_tiles);
+  kern<<<grid, L::kThreads, L::kDynBytes, s>>>(p, tm, tm_dev, num_m, num_tiles);
   profile_mark(0, false, s);
-  FA_CUDA(cudaGetLastError());
+  const cudaError_t launch_err = cudaGetLastError();
+  if (tm_dev) cudaFreeAsync(tm_dev, s);
+  FA_CUDA(launch_err);
   note_launch(2);
 }
 
@@ -648,6 +661,13 @@ bool sm100_fwd2_eligible(const Params &p) {
 }
 
 void sm100_fwd2(const Params &p, cudaStream_t s) {
+  // experiment switch: FA_B200_FWD2_QT=1 runs head dims <= 128 with ONE Q tile per CTA (S double-buffered over key blocks)
+  static const bool one_tile = [] { const char *e = getenv("FA_B200_FWD2_QT"); return e && e[0] == '1'; }();
+  if (one_tile && p.d <= 128) {
+    if (p.d <= 64) { if (p.is_bf16) launch_fwd2<64, true, 1>(p, s); else launch_fwd2<64, false, 1>(p, s); }
+    else { if (p.is_bf16) launch_fwd2<128, true, 1>(p, s); else launch_fwd2<128, false, 1>(p, s); }
+    return;
+  }
   if (p.d <= 64) { if (p.is_bf16) launch_fwd2<64, true>(p, s); else launch_fwd2<64, false>(p, s); }
   else if (p.d <= 128) { if (p.is_bf16) launch_fwd2<128, true>(p, s); else launch_fwd2<128, false>(p, s); }
   else if (p.d <= 192) { if (p.is_bf16) launch_fwd2<192, true>(p, s); else launch_fwd2<192, false>(p, s); }
