@@ -19,6 +19,18 @@
 #include "common.h"
 #include "sm100.cuh"
 
+#ifdef FA_TRACE
+// Timeline probe (variant builds only, tools/trace_fwd.py): CTA 0 records clock64() at the hand-over points of its first
+// key blocks -- role 0/1 = softmax warpgroup of Q tile 0/1 (first warp), role 2 = MMA issuer.
+__device__ unsigned long long fa_trace_buf[3][96][8];
+#define FA_TR(role, blk, ev) do { if (blockIdx.x == 0 && lane == 0 && (blk) < 96u) fa_trace_buf[role][blk][ev] = clock64(); } while (0)
+extern "C" int fa_b200_trace_dump(unsigned long long *host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, fa_trace_buf, sizeof(fa_trace_buf));
+}
+#else
+#define FA_TR(role, blk, ev) do { } while (0)
+#endif
+
 namespace fa {
 namespace {
 
@@ -543,10 +555,13 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
             if (cur.a[t]) {
+              FA_TR(2, pcnt[t], t * 4 + 0);
               mbar_wait(bar(B_PHALF + t), pcnt[t] & 1);
+              FA_TR(2, pcnt[t], t * 4 + 1);
               tc_fence_after();
               issue_pv_half(t, vst, 0, !first[t]);
               mbar_wait(bar(B_PFULL + t), pcnt[t] & 1);
+              FA_TR(2, pcnt[t], t * 4 + 2);
               ++pcnt[t];
               tc_fence_after();
               issue_pv_half(t, vst, 1, !first[t]);
@@ -561,6 +576,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
               need_q(t);
               tc_fence_after();
               issue_s(t, nkst);
+              FA_TR(2, pcnt[t] - 1, t * 4 + 3);
             }
           }
           commit(bar(B_KVEMPTY + vst));
@@ -671,13 +687,16 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
       while (seq.next(blk)) {
         if (!blk.a[t]) continue;
         const int j = blk.j;
+        if (warp % 4 == 0) FA_TR(t, scnt, 0);
         mbar_wait(bar(B_SFULL + t), scnt & 1);
+        if (warp % 4 == 0) FA_TR(t, scnt, 1);
         ++scnt;
         tc_fence_after();
         uint32_t s[4][32];
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
         tmem_wait_ld();
+        if (warp % 4 == 0) FA_TR(t, scnt - 1, 2);
         const int c0 = j * kBN;
         if constexpr (kCap) {
 #pragma unroll
@@ -817,6 +836,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
           }
         }
         const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
+        if (warp % 4 == 0) FA_TR(t, scnt - 1, 3);
         const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
         uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
 #pragma unroll
@@ -851,6 +871,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(bar(B_PHALF + t));
+            if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
           }
         }
         {
@@ -861,6 +882,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar(B_PFULL + t));
+        if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
         ++nb;
       }
       if (nb == 0) {
