@@ -644,6 +644,9 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
     const float scale_nat = kCap ? p.softcap : p.softmax_scale;
     const float scale_log2 = scale_nat * kLog2e;
     const float pre_cap = kCap ? p.softmax_scale / p.softcap : 0.f;
+    constexpr bool kPipe = !kCap && !kMask && !kDrop;       // streamed S chunks: plain and FlashMask instantiations
+    const float thr_nat = kRescaleThreshold / scale_log2;   // the rescale threshold (2^8) in units of raw scores
+    (void)thr_nat;
     uint32_t scnt = 0, ocnt = 0;
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     BlockSeq<kFM> seq;
@@ -693,53 +696,16 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
         ++scnt;
         tc_fence_after();
         uint32_t s[4][32];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
-        tmem_wait_ld();
-        if (warp % 4 == 0) FA_TR(t, scnt - 1, 2);
         const int c0 = j * kBN;
-        if constexpr (kCap) {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              float y;
-              asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(s[c][i]) * pre_cap));
-              s[c][i] = __float_as_uint(y);
-            }
-        }
-        if constexpr (kMask) {
-          // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
-          const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
-                              c0 + kBN <= p.seqlen_k;
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 8) {
-              const int col = c0 + c * 32 + i;
-              if (vec_ok) {
-                const uint4 mv = *reinterpret_cast<const uint4 *>(mask_row + col);
-                const T *me = reinterpret_cast<const T *>(&mv);
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                  s[c][i + e] = __float_as_uint(fmaf(to_float(me[e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
-              } else {
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                  if (col + e < p.seqlen_k)
-                    s[c][i + e] = __float_as_uint(fmaf(to_float(mask_row[col + e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
-              }
-            }
-          }
-        }
         const bool full = (c0 + kBN <= ti.sk) && (!mc.causal || c0 + kBN - 1 <= r0 + shiftc) &&
                           (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
                           (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) &&
                           (kFM ? !blk.pm[t] : (mc.lts == nullptr));
+        // mask bits of this thread's row for the 128 columns of the block (needs no S): boundary / flashmask blocks only
+        uint32_t mb[4] = {0u, 0u, 0u, 0u};
         if (!full) {
           // boundary / flashmask blocks: the generic mask rule runs in a rolled loop (emitted once, keeps the hot loop
           // inside the instruction cache); the unrolled pass below only applies the resulting bit mask
-          uint32_t mb[4];
           if (mc.lts == nullptr || kFM) {  // seqlen tail / causal / window: the visible columns of a row form an interval
             int vlo, vhi;
             visible_cols(mc, row, vlo, vhi);
@@ -797,92 +763,237 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
             for (int i = 0; i < kBN; ++i)
               if (is_masked(mc, row, c0 + i)) mb[i >> 5] |= 1u << (i & 31);
           }
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
         }
-        float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+        // ---- streamed path -------------------------------------------------------------------------------------
+        // TMEM -> register loads run at ~64-90 bytes/clk per SM (measured with the FA_TRACE build: a 64 KB S tile takes
+        // 700-800 cycles), about as long as the tile's MMAs.  With the reference maximum already known (every block but
+        // the first: the lazy rescale keeps m_ref unless it would be exceeded by more than 2^8) nothing forces the
+        // exponentials to wait for the whole row: S is fetched in four 32-column chunks, chunk c+1 streams in while
+        // chunk c is checked against the threshold and exponentiated.  If any row of the warp exceeds the threshold
+        // the block is redone on the full path below (first block of a tile, and whenever the maximum jumps).
+        // The first half of P is only announced after all four chunks have passed the check.
+        bool done = false;
+        if constexpr (kPipe) {
+          int nld = 0;
+          if (!__any_sync(0xffffffffu, nb == 0 || m_ref == -CUDART_INF_F)) {
+            const float lim = m_ref + thr_nat;
+            const float msc_f = m_ref * scale_log2;
+            const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc_f, -msc_f);
+            uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
+            auto mask_chunk = [&](auto C) {
+              constexpr int c = decltype(C)::value;
+              if (!full) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          mx0 = fmaxf(mx0, __uint_as_float(s[0][i]));
-          mx1 = fmaxf(mx1, __uint_as_float(s[1][i]));
-          mx2 = fmaxf(mx2, __uint_as_float(s[2][i]));
-          mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
-        }
-        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-        if (nb == 0) {
-          m_ref = mx;
-        } else {
-          const bool need = (mx > m_ref) && ((mx - m_ref) * scale_log2 > kRescaleThreshold || m_ref == -CUDART_INF_F);
-          if (__any_sync(0xffffffffu, need)) {
-            // the previous PV of this tile must have landed in O before it is rescaled
-            mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
-            tc_fence_after();
-            const float m_new = fmaxf(m_ref, mx);
-            const float corr = (m_new == -CUDART_INF_F) ? 1.f : ex2((m_ref - m_new) * scale_log2);
-            l *= corr;
-            m_ref = m_new;
+                for (int i = 0; i < 32; ++i)
+                  if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
+              }
+            };
+            auto over = [&](auto C) {     // does any row of the warp exceed the threshold in chunk c?
+              constexpr int c = decltype(C)::value;
+              float m0 = __uint_as_float(s[c][0]), m1 = __uint_as_float(s[c][1]);
 #pragma unroll
-            for (int c = 0; c < HD / 32; ++c) {
-              uint32_t o[32];
-              tmem_ld32(tO + c * 32, o);
+              for (int i = 2; i < 32; i += 2) {
+                m0 = fmaxf(m0, __uint_as_float(s[c][i]));
+                m1 = fmaxf(m1, __uint_as_float(s[c][i + 1]));
+              }
+              return __any_sync(0xffffffffu, fmaxf(m0, m1) > lim) != 0;
+            };
+            auto exp_chunk = [&](auto C) {
+              constexpr int c = decltype(C)::value;
+              uint32_t pk[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
+                float p0, p1;
+                if (i % 4 == 3) {          // every fourth pair: polynomial on the FMA pipe
+                  exp2_poly2(x2, p0, p1);
+                } else {
+                  float x0, x1;
+                  unpk2(x2, x0, x1);
+                  p0 = ex2(x0); p1 = ex2(x1);
+                }
+                if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
+                pk[i] = pack2<kBf16>(p0, p1);
+              }
+              tmem_st16(tS + c * 16, pk);
+            };
+            using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
+            using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
+            tmem_ld32(tS, s[0]);
+            tmem_wait_ld();
+            tmem_ld32(tS + 32, s[1]);
+            nld = 2;
+            mask_chunk(I0{});
+            if (!over(I0{})) {
+              exp_chunk(I0{});
               tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
-              tmem_st32(tO + c * 32, o);
+              tmem_ld32(tS + 64, s[2]);
+              nld = 3;
+              mask_chunk(I1{});
+              if (!over(I1{})) {
+                exp_chunk(I1{});
+                tmem_wait_ld();
+                tmem_ld32(tS + 96, s[3]);
+                nld = 4;
+                mask_chunk(I2{});
+                if (!over(I2{})) {
+                  tmem_wait_ld();
+                  mask_chunk(I3{});
+                  if (!over(I3{})) {
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(bar(B_PHALF + t));
+                    if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
+                    exp_chunk(I2{});
+                    exp_chunk(I3{});
+                    float a0, a1;
+                    unpk2(fadd2(suma, sumb), a0, a1);
+                    l += a0 + a1;
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(bar(B_PFULL + t));
+                    if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
+                    done = true;
+                  }
+                }
+              }
             }
           }
-        }
-        const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
-        if (warp % 4 == 0) FA_TR(t, scnt - 1, 3);
-        const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
-        uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t pk[16];
-          uint4 rnd = make_uint4(0, 0, 0, 0);
-          (void)rnd;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
-            float p0, p1;
-            if (i % 4 == 3) {          // every fourth pair: polynomial on the FMA pipe
-              exp2_poly2(x2, p0, p1);
-            } else {
-              float x0, x1;
-              unpk2(x2, x0, x1);
-              p0 = ex2(x0); p1 = ex2(x1);
-            }
-            if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
-            if constexpr (kDrop) {
-              if (i % 8 == 0)
-                rnd = philox4x32_10(dctx.seed, dctx.row_base + (uint32_t)((blk.j * kBN + c * 32 + 2 * i) >> 4), dctx.offset);
-              const int e = (2 * i) & 15;                       // position of the pair inside its 16-column group
-              const uint32_t w = e < 4 ? rnd.x : e < 8 ? rnd.y : e < 12 ? rnd.z : rnd.w;
-              if (((w >> ((e & 3) * 8)) & 0xffu) > dctx.threshold) p0 = 0.f;
-              if (((w >> (((e + 1) & 3) * 8)) & 0xffu) > dctx.threshold) p1 = 0.f;
-            }
-            pk[i] = pack2<kBf16>(p0, p1);
+          if (!done) {   // full path: all four chunks in registers (chunks 0 and 1 may already be overwritten in TMEM by P)
+            if (nld == 0) { tmem_ld32(tS, s[0]); tmem_ld32(tS + 32, s[1]); }
+            if (nld <= 2) tmem_ld32(tS + 64, s[2]);
+            if (nld <= 3) tmem_ld32(tS + 96, s[3]);
+            tmem_wait_ld();
           }
-          tmem_st16(tS + c * 16, pk);
-          if (c == 1) {   // the first 64 columns of P are in TMEM: let the issuer start the first half of PV
-            tmem_wait_st();
-            tc_fence_before();
-            mbar_arrive(bar(B_PHALF + t));
-            if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+          tmem_wait_ld();
+        }
+        if (warp % 4 == 0) FA_TR(t, scnt - 1, 2);
+        if (!done) {
+          if constexpr (kCap) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                float y;
+                asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(s[c][i]) * pre_cap));
+                s[c][i] = __float_as_uint(y);
+              }
           }
+          if constexpr (kMask) {
+            // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
+            const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
+                                c0 + kBN <= p.seqlen_k;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                const int col = c0 + c * 32 + i;
+                if (vec_ok) {
+                  const uint4 mv = *reinterpret_cast<const uint4 *>(mask_row + col);
+                  const T *me = reinterpret_cast<const T *>(&mv);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e)
+                    s[c][i + e] = __float_as_uint(fmaf(to_float(me[e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+                } else {
+#pragma unroll
+                  for (int e = 0; e < 8; ++e)
+                    if (col + e < p.seqlen_k)
+                      s[c][i + e] = __float_as_uint(fmaf(to_float(mask_row[col + e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+                }
+              }
+            }
+          }
+          if (!full) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
+          }
+          float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            mx0 = fmaxf(mx0, __uint_as_float(s[0][i]));
+            mx1 = fmaxf(mx1, __uint_as_float(s[1][i]));
+            mx2 = fmaxf(mx2, __uint_as_float(s[2][i]));
+            mx3 = fmaxf(mx3, __uint_as_float(s[3][i]));
+          }
+          const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+          if (nb == 0) {
+            m_ref = mx;
+          } else {
+            const bool need = (mx > m_ref) && ((mx - m_ref) * scale_log2 > kRescaleThreshold || m_ref == -CUDART_INF_F);
+            if (__any_sync(0xffffffffu, need)) {
+              // the previous PV of this tile must have landed in O before it is rescaled
+              mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
+              tc_fence_after();
+              const float m_new = fmaxf(m_ref, mx);
+              const float corr = (m_new == -CUDART_INF_F) ? 1.f : ex2((m_ref - m_new) * scale_log2);
+              l *= corr;
+              m_ref = m_new;
+#pragma unroll
+              for (int c = 0; c < HD / 32; ++c) {
+                uint32_t o[32];
+                tmem_ld32(tO + c * 32, o);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+                tmem_st32(tO + c * 32, o);
+              }
+            }
+          }
+          const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
+          if (warp % 4 == 0) FA_TR(t, scnt - 1, 3);
+          const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
+          uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t pk[16];
+            uint4 rnd = make_uint4(0, 0, 0, 0);
+            (void)rnd;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
+              float p0, p1;
+              if (i % 4 == 3) {          // every fourth pair: polynomial on the FMA pipe
+                exp2_poly2(x2, p0, p1);
+              } else {
+                float x0, x1;
+                unpk2(x2, x0, x1);
+                p0 = ex2(x0); p1 = ex2(x1);
+              }
+              if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
+              if constexpr (kDrop) {
+                if (i % 8 == 0)
+                  rnd = philox4x32_10(dctx.seed, dctx.row_base + (uint32_t)((blk.j * kBN + c * 32 + 2 * i) >> 4), dctx.offset);
+                const int e = (2 * i) & 15;                       // position of the pair inside its 16-column group
+                const uint32_t w = e < 4 ? rnd.x : e < 8 ? rnd.y : e < 12 ? rnd.z : rnd.w;
+                if (((w >> ((e & 3) * 8)) & 0xffu) > dctx.threshold) p0 = 0.f;
+                if (((w >> (((e + 1) & 3) * 8)) & 0xffu) > dctx.threshold) p1 = 0.f;
+              }
+              pk[i] = pack2<kBf16>(p0, p1);
+            }
+            tmem_st16(tS + c * 16, pk);
+            if (c == 1) {   // the first 64 columns of P are in TMEM: let the issuer start the first half of PV
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar(B_PHALF + t));
+              if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
+            }
+          }
+          {
+            float a0, a1;
+            unpk2(fadd2(suma, sumb), a0, a1);
+            l += a0 + a1;
+          }
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar(B_PFULL + t));
+          if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
         }
-        {
-          float a0, a1;
-          unpk2(fadd2(suma, sumb), a0, a1);
-          l += a0 + a1;
-        }
-        tmem_wait_st();
-        tc_fence_before();
-        mbar_arrive(bar(B_PFULL + t));
-        if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
         ++nb;
       }
       if (nb == 0) {
@@ -1047,9 +1158,10 @@ template <int HD, bool kBf16> void dispatch_fwd(const Params &p, cudaStream_t s)
 }  // namespace
 
 void sm100_fwd(const Params &p, cudaStream_t s) {
-  // plain calls (and every head dim above 128) take the split-row kernel of sm100_fwd2.cu; FA_B200_FWD2=0 keeps the
-  // one-thread-per-row kernel for head dims <= 128 (A/B measurements)
-  static const bool use_fwd2 = [] { const char *e = getenv("FA_B200_FWD2"); return !(e && e[0] == '0'); }();
+  // every head dim above 128 takes the split-row kernel of sm100_fwd2.cu.  For head dims <= 128 the one-thread-per-row
+  // kernel below is faster (measured on C3: 1123 vs 1028 TFLOPS with two Q tiles per CTA, 1081 with one);
+  // FA_B200_FWD2=1 selects the split-row kernel there too (A/B measurements)
+  static const bool use_fwd2 = [] { const char *e = getenv("FA_B200_FWD2"); return e && e[0] == '1'; }();
   if (sm100_fwd2_eligible(p) && (p.d > 128 || use_fwd2)) { sm100_fwd2(p, s); return; }
   if (p.d <= 64) { if (p.is_bf16) dispatch_fwd<64, true>(p, s); else dispatch_fwd<64, false>(p, s); }
   else { if (p.is_bf16) dispatch_fwd<128, true>(p, s); else dispatch_fwd<128, false>(p, s); }

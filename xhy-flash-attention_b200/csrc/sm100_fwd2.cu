@@ -191,6 +191,11 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
     }
     fence_mbar_init();
   }
+#ifdef FA_POISON
+  // debug variant: fill the operand tiles with NaN patterns so that any byte TMA does not write shows up in the output
+  for (int i = threadIdx.x; i < L::kXchOff / 16; i += L::kThreads) sts128(sbase + i * 16, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+  fence_proxy_async_smem();
+#endif
   if (warp == kSmWarps) tmem_alloc<512>(smem_u32(tmem_slot));
   if (warp == kSmWarps + 1 && lane == 0) {
     if (tm_dev) { tma_acquire_desc(&tm.q); tma_acquire_desc(&tm.k); tma_acquire_desc(&tm.v); }
@@ -300,7 +305,9 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
             umma_ts(tmem + 2 * kBN + t * HD, tmem + slot * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kBoxBytes, 1024),
                     idesc_o, (accumulate || k > 0) ? 1u : 0u);
           }
-          if (half == 1) umma_commit(bar(B_OFULL + t));
+          // completion of this P V.  One Q tile: signalled per S SLOT, because there S runs two key blocks ahead of P V and
+          // a single barrier could be two phases ahead of a waiter (a parity wait cannot tell phase n from phase n + 2)
+          if (half == 1) umma_commit(bar(B_OFULL + (kQT == 2 ? t : slot)));
         }
         __syncwarp();
       };
@@ -490,7 +497,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
           const bool need = (mx > m_ref) && ((mx - m_ref) * scale_log2 > kRescaleThreshold || m_ref == -CUDART_INF_F);
           if (__any_sync(0xffffffffu, need)) {
             // the previous P V of this tile must have landed in O before it is rescaled
-            mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
+            if constexpr (kQT == 2) mbar_wait(bar(B_OFULL + t), (ocnt + nb - 1) & 1);
+            else mbar_wait(bar(B_OFULL + ((g - 1) & 1u)), ((g - 1) >> 1) & 1u);   // block g - 1: slot (g-1)&1, its (g-1)>>1-th use
             tc_fence_after();
             const float m_new = fmaxf(m_ref, mx);
             const float corr = (m_new == -CUDART_INF_F) ? 1.f : ex2((m_ref - m_new) * scale_log2);
@@ -551,7 +559,12 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
       }
       // ---------------- epilogue ----------------
       xsum[(t * 2 + hf) * kBM + r_in_tile] = l;
-      mbar_wait(bar(B_OFULL + t), (ocnt + nb_total - 1) & 1);
+      if constexpr (kQT == 2) {
+        mbar_wait(bar(B_OFULL + t), (ocnt + nb_total - 1) & 1);
+      } else {   // g already counts this tile's blocks: the last two P V are blocks g - 2 and g - 1 (P V complete in order)
+        if (nb_total > 1) mbar_wait(bar(B_OFULL + ((g - 2) & 1u)), ((g - 2) >> 1) & 1u);
+        mbar_wait(bar(B_OFULL + ((g - 1) & 1u)), ((g - 1) >> 1) & 1u);
+      }
       ocnt += nb_total;
       tc_fence_after();
       named_bar_sync(1 + t, 2 * kBM);
