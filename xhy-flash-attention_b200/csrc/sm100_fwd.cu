@@ -27,8 +27,12 @@ __device__ unsigned long long fa_trace_buf[3][96][8];
 extern "C" int fa_b200_trace_dump(unsigned long long *host_out) {
   return (int)cudaMemcpyFromSymbol(host_out, fa_trace_buf, sizeof(fa_trace_buf));
 }
+// the clock is read only after `val` is available (the asm takes it as an input): times a data arrival, not an issue
+#define FA_TR_DEP(role, blk, ev, val) do { if (blockIdx.x == 0 && lane == 0 && (blk) < 96u) { unsigned long long t__; \
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t__) : "r"(val)); fa_trace_buf[role][blk][ev] = t__; } } while (0)
 #else
 #define FA_TR(role, blk, ev) do { } while (0)
+#define FA_TR_DEP(role, blk, ev, val) do { } while (0)
 #endif
 
 namespace fa {
@@ -264,6 +268,11 @@ __device__ __forceinline__ void fm_scan_tile(const Params &p, const TileInfo &ti
   publish(-1, 0u, 0u, 0u, 0u);   // end of tile
 }
 
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -644,9 +653,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
     const float scale_nat = kCap ? p.softcap : p.softmax_scale;
     const float scale_log2 = scale_nat * kLog2e;
     const float pre_cap = kCap ? p.softmax_scale / p.softcap : 0.f;
-    constexpr bool kPipe = !kCap && !kMask && !kDrop;       // streamed S chunks: plain and FlashMask instantiations
-    const float thr_nat = kRescaleThreshold / scale_log2;   // the rescale threshold (2^8) in units of raw scores
-    (void)thr_nat;
+    constexpr bool kPipe = !kCap && !kMask && !kDrop;       // fast path of the block loop: plain and FlashMask instantiations
     uint32_t scnt = 0, ocnt = 0;
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     BlockSeq<kFM> seq;
@@ -696,16 +703,53 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
         ++scnt;
         tc_fence_after();
         uint32_t s[4][32];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
+        tmem_wait_ld();
+        if (warp % 4 == 0) FA_TR_DEP(t, scnt - 1, 2, s[3][31]);   // the last loaded column has arrived
         const int c0 = j * kBN;
+        if constexpr (kCap) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float y;
+              asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(s[c][i]) * pre_cap));
+              s[c][i] = __float_as_uint(y);
+            }
+        }
+        if constexpr (kMask) {
+          // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
+          const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
+                              c0 + kBN <= p.seqlen_k;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              const int col = c0 + c * 32 + i;
+              if (vec_ok) {
+                const uint4 mv = *reinterpret_cast<const uint4 *>(mask_row + col);
+                const T *me = reinterpret_cast<const T *>(&mv);
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  s[c][i + e] = __float_as_uint(fmaf(to_float(me[e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+              } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (col + e < p.seqlen_k)
+                    s[c][i + e] = __float_as_uint(fmaf(to_float(mask_row[col + e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
+              }
+            }
+          }
+        }
         const bool full = (c0 + kBN <= ti.sk) && (!mc.causal || c0 + kBN - 1 <= r0 + shiftc) &&
                           (mc.wr < 0 || c0 + kBN - 1 <= r0 + mc.shift + mc.wr) &&
                           (mc.wl < 0 || c0 >= r0 + kBM - 1 + mc.shift - mc.wl) &&
                           (kFM ? !blk.pm[t] : (mc.lts == nullptr));
-        // mask bits of this thread's row for the 128 columns of the block (needs no S): boundary / flashmask blocks only
-        uint32_t mb[4] = {0u, 0u, 0u, 0u};
         if (!full) {
           // boundary / flashmask blocks: the generic mask rule runs in a rolled loop (emitted once, keeps the hot loop
           // inside the instruction cache); the unrolled pass below only applies the resulting bit mask
+          uint32_t mb[4];
           if (mc.lts == nullptr || kFM) {  // seqlen tail / causal / window: the visible columns of a row form an interval
             int vlo, vhi;
             visible_cols(mc, row, vlo, vhi);
@@ -763,156 +807,86 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
             for (int i = 0; i < kBN; ++i)
               if (is_masked(mc, row, c0 + i)) mb[i >> 5] |= 1u << (i & 31);
           }
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
         }
-        // ---- streamed path -------------------------------------------------------------------------------------
-        // TMEM -> register loads run at ~64-90 bytes/clk per SM (measured with the FA_TRACE build: a 64 KB S tile takes
-        // 700-800 cycles), about as long as the tile's MMAs.  With the reference maximum already known (every block but
-        // the first: the lazy rescale keeps m_ref unless it would be exceeded by more than 2^8) nothing forces the
-        // exponentials to wait for the whole row: S is fetched in four 32-column chunks, chunk c+1 streams in while
-        // chunk c is checked against the threshold and exponentiated.  If any row of the warp exceeds the threshold
-        // the block is redone on the full path below (first block of a tile, and whenever the maximum jumps).
-        // The first half of P is only announced after all four chunks have passed the check.
+        // ---- fast path: exponentials against the EXISTING reference maximum, row maximum computed alongside ----
+        // Timeline probe (FA_TRACE build, C3): of the 2150 cycles a softmax warp spends per key block, ~750 went into the
+        // row-maximum pass, during which MUFU idles; the exponentials that follow are MUFU-bound.  The lazy-rescale rule
+        // only needs "block maximum <= m_ref + 2^8 (log2 domain)", so for every block but a tile's first the
+        // exponentials of the first 64 columns start at once against m_ref and the 64 FMNMX3 of the maximum are
+        // interleaved with them (independent chains that fill MUFU's issue gaps).  The check is made before the first
+        // half of P is announced; if some row of the warp fails it, the block is redone on the full path below (S is
+        // still in registers; only P columns that nobody has been told about were written).
         bool done = false;
         if constexpr (kPipe) {
-          int nld = 0;
           if (!__any_sync(0xffffffffu, nb == 0 || m_ref == -CUDART_INF_F)) {
-            const float lim = m_ref + thr_nat;
             const float msc_f = m_ref * scale_log2;
             const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc_f, -msc_f);
             uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
-            auto mask_chunk = [&](auto C) {
-              constexpr int c = decltype(C)::value;
-              if (!full) {
+            float mxa = -CUDART_INF_F, mxb = -CUDART_INF_F;
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                  if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
-              }
-            };
-            auto over = [&](auto C) {     // does any row of the warp exceed the threshold in chunk c?
-              constexpr int c = decltype(C)::value;
-              float m0 = __uint_as_float(s[c][0]), m1 = __uint_as_float(s[c][1]);
-#pragma unroll
-              for (int i = 2; i < 32; i += 2) {
-                m0 = fmaxf(m0, __uint_as_float(s[c][i]));
-                m1 = fmaxf(m1, __uint_as_float(s[c][i + 1]));
-              }
-              return __any_sync(0xffffffffu, fmaxf(m0, m1) > lim) != 0;
-            };
-            auto exp_chunk = [&](auto C) {
-              constexpr int c = decltype(C)::value;
+            for (int c = 0; c < 2; ++c) {
               uint32_t pk[16];
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
                 const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
                 float p0, p1;
-                if (i % 4 == 3) {          // every fourth pair: polynomial on the FMA pipe
+                if (i % 4 == 3) {
                   exp2_poly2(x2, p0, p1);
                 } else {
                   float x0, x1;
                   unpk2(x2, x0, x1);
                   p0 = ex2(x0); p1 = ex2(x1);
                 }
+                // the row maximum over all four chunks rides along: two 3-input maxima per pair of exponentials
+                mxa = fmax3(mxa, __uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1]));
+                mxb = fmax3(mxb, __uint_as_float(s[c + 2][2 * i]), __uint_as_float(s[c + 2][2 * i + 1]));
                 if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
                 pk[i] = pack2<kBf16>(p0, p1);
               }
               tmem_st16(tS + c * 16, pk);
-            };
-            using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
-            using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
-            tmem_ld32(tS, s[0]);
-            tmem_wait_ld();
-            tmem_ld32(tS + 32, s[1]);
-            nld = 2;
-            mask_chunk(I0{});
-            if (!over(I0{})) {
-              exp_chunk(I0{});
-              tmem_wait_ld();
-              tmem_ld32(tS + 64, s[2]);
-              nld = 3;
-              mask_chunk(I1{});
-              if (!over(I1{})) {
-                exp_chunk(I1{});
-                tmem_wait_ld();
-                tmem_ld32(tS + 96, s[3]);
-                nld = 4;
-                mask_chunk(I2{});
-                if (!over(I2{})) {
-                  tmem_wait_ld();
-                  mask_chunk(I3{});
-                  if (!over(I3{})) {
-                    tmem_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(bar(B_PHALF + t));
-                    if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
-                    exp_chunk(I2{});
-                    exp_chunk(I3{});
-                    float a0, a1;
-                    unpk2(fadd2(suma, sumb), a0, a1);
-                    l += a0 + a1;
-                    tmem_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(bar(B_PFULL + t));
-                    if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
-                    done = true;
+            }
+            const float mxf = fmaxf(mxa, mxb);
+            if (!__any_sync(0xffffffffu, (mxf - m_ref) * scale_log2 > kRescaleThreshold)) {
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar(B_PHALF + t));
+              if (warp % 4 == 0) FA_TR(t, scnt - 1, 4);
+#pragma unroll
+              for (int c = 2; c < 4; ++c) {
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
+                  float p0, p1;
+                  if (i % 4 == 3) {
+                    exp2_poly2(x2, p0, p1);
+                  } else {
+                    float x0, x1;
+                    unpk2(x2, x0, x1);
+                    p0 = ex2(x0); p1 = ex2(x1);
                   }
+                  if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
+                  pk[i] = pack2<kBf16>(p0, p1);
                 }
+                tmem_st16(tS + c * 16, pk);
               }
+              float a0, a1;
+              unpk2(fadd2(suma, sumb), a0, a1);
+              l += a0 + a1;
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar(B_PFULL + t));
+              if (warp % 4 == 0) FA_TR(t, scnt - 1, 5);
+              done = true;
             }
           }
-          if (!done) {   // full path: all four chunks in registers (chunks 0 and 1 may already be overwritten in TMEM by P)
-            if (nld == 0) { tmem_ld32(tS, s[0]); tmem_ld32(tS + 32, s[1]); }
-            if (nld <= 2) tmem_ld32(tS + 64, s[2]);
-            if (nld <= 3) tmem_ld32(tS + 96, s[3]);
-            tmem_wait_ld();
-          }
-        } else {
-#pragma unroll
-          for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, s[c]);
-          tmem_wait_ld();
         }
-        if (warp % 4 == 0) FA_TR(t, scnt - 1, 2);
         if (!done) {
-          if constexpr (kCap) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-#pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                float y;
-                asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(s[c][i]) * pre_cap));
-                s[c][i] = __float_as_uint(y);
-              }
-          }
-          if constexpr (kMask) {
-            // (fetching the 128 mask values before the wait for S was tried: 64 more live registers, spills, slower)
-            const bool vec_ok = (p.seqlen_k % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.attn_mask) & 15) == 0) &&
-                                c0 + kBN <= p.seqlen_k;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 8) {
-                const int col = c0 + c * 32 + i;
-                if (vec_ok) {
-                  const uint4 mv = *reinterpret_cast<const uint4 *>(mask_row + col);
-                  const T *me = reinterpret_cast<const T *>(&mv);
-#pragma unroll
-                  for (int e = 0; e < 8; ++e)
-                    s[c][i + e] = __float_as_uint(fmaf(to_float(me[e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
-                } else {
-#pragma unroll
-                  for (int e = 0; e < 8; ++e)
-                    if (col + e < p.seqlen_k)
-                      s[c][i + e] = __float_as_uint(fmaf(to_float(mask_row[col + e]), p.unscale_softmax, __uint_as_float(s[c][i + e])));
-                }
-              }
-            }
-          }
-          if (!full) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-#pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if ((mb[c] >> i) & 1u) s[c][i] = __float_as_uint(-CUDART_INF_F);
-          }
           float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
@@ -946,7 +920,8 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
             }
           }
           const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
-          if (warp % 4 == 0) FA_TR(t, scnt - 1, 3);
+          if (warp % 4 == 0) FA_TR_DEP(t, scnt - 1, 3, __float_as_uint(msc));   // the row maximum is known
+          if (warp % 4 == 0) FA_TR_DEP(t, scnt - 1, 6, __float_as_uint(mx));
           const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
           uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
 #pragma unroll
