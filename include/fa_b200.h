@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 4
+#define FA_B200_ABI_VERSION 5
 
 /* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
  * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
@@ -123,6 +123,11 @@ typedef struct fa_b200_params {
   const int32_t *seqused_q;       /* (b) int32 or NULL: only the first seqused_q[i] query rows of batch element i are
                                      attended (csrc/flashmask_v2/seqlen.h:17-53); rows beyond are left untouched in out,
                                      lse, dq.  Bottom-right alignment then uses seqused_q[i] as the query length. */
+  /* ---- per-batch split counts (ABI v5; reference: num_splits_dynamic_ptr, csrc/flash_attn_v3/flash.h:96-125,
+   *      filled by prepare_varlen_num_blocks, flash_prepare_scheduler.cu:15-124) ---- */
+  const int32_t *num_splits_dynamic; /* (b) int32 or NULL: batch element i is cut into num_splits_dynamic[i] <= num_splits
+                                        key ranges; the partial results of the remaining splits are written as empty
+                                        (lse = -inf) and the combine skips them.  fa_b200_prepare_num_splits fills it. */
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */
@@ -146,6 +151,13 @@ int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seql
  * 128-key blocks; picks the split count that minimises waves x (blocks per split + fixed per-CTA cost).  The reference
  * heuristic above is kept for callers that want its exact answer; this one is what flash_attn_with_kvcache uses. */
 int fa_b200_decode_num_splits(int batch, int num_heads_k, int seqlen_k, int num_sm);
+
+/* Per-batch split counts for a batch of unequal lengths (cu_seqlens_k / seqused_k / leftpad_k): restates
+ * prepare_varlen_num_blocks (csrc/flash_attn_v3/flash_prepare_scheduler.cu:15-124) for this library's tiles --
+ * blocks_per_sm = ceil(1.1 * heads_k * sum_b m_blocks(b) * n_blocks(b) / num_sm),
+ * out[b] = clamp(ceil(n_blocks(b) / blocks_per_sm), 1, p->num_splits), with 16 packed query rows per m block and 128 keys
+ * per n block.  One launch of one CTA; batch <= 1024. */
+bool fa_b200_prepare_num_splits(const fa_b200_params *p, int32_t *num_splits_dynamic_out, int num_sm, cudaStream_t stream);
 
 /* Append new K/V rows into the cache at position seqused_k[b] (flash_attn_with_kvcache's k=/v= arguments;
  * reference: csrc/flash_attn_v3/mainloop_fwd_sm90_tma_gmma_ws.hpp:1542 store_kv_new). */

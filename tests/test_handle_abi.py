@@ -346,3 +346,86 @@ def test_handle_seqused_q(fa, causal, with_k):
         for t_ in (dk[i, nk:], dv[i, nk:]):            # keys beyond seqused_k receive no gradient: untouched or zero
             assert ((t_ == sentinel) | (t_ == 0)).all()
     hf.close(); hb.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dynamic", [False, True])
+@pytest.mark.parametrize("varlen_q", [False, True])
+def test_handle_varlen_split_decode(fa, varlen_q, dynamic):
+    """Split-KV decode over PACKED K/V (cu_seqlens_k) -- optionally packed queries too -- with per-batch split counts:
+    num_splits_dynamic_ptr is filled by the library (prepare_varlen_num_blocks, flash_prepare_scheduler.cu:15-124) unless
+    skip_scheduler_metadata_computation is set; short sequences get fewer splits, the surplus partials are empty."""
+    from tests._util import check_2x
+    lib = capi.load()
+    torch.manual_seed(3)
+    dev = "cuda"
+    lens_k = [4000, 150, 1290, 64]
+    lens_q = [2, 1, 3, 1] if varlen_q else [1, 1, 1, 1]
+    b, h, hk, d, splits = len(lens_k), 8, 2, 128, 5
+    tk, tq, msq = sum(lens_k), sum(lens_q), max(lens_q)
+    k, v = [torch.randn(tk, hk, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]
+    cu_k = torch.tensor([0] + torch.tensor(lens_k).cumsum(0).tolist(), device=dev, dtype=torch.int32)
+    cu_q = torch.tensor([0] + torch.tensor(lens_q).cumsum(0).tolist(), device=dev, dtype=torch.int32)
+    if varlen_q:
+        q = torch.randn(tq, h, d, device=dev, dtype=torch.bfloat16)
+        lse = torch.full((h, tq), float("nan"), device=dev, dtype=torch.float32)
+    else:
+        q = torch.randn(b, 1, h, d, device=dev, dtype=torch.bfloat16)
+        lse = torch.full((b, h, 1), float("nan"), device=dev, dtype=torch.float32)
+    o = torch.full_like(q, float("nan"))
+    oacc = torch.empty(splits, b, msq, h, d, device=dev, dtype=torch.float32)
+    lacc = torch.empty(splits, b, h, msq, device=dev, dtype=torch.float32)
+    dyn = torch.full((b,), -1, device=dev, dtype=torch.int32)
+    hf = Handle(lib, "fa3", "fwd")
+    for name, t, packed in (("q", q, varlen_q), ("k", k, True), ("v", v, True), ("o", o, varlen_q)):
+        st = (0, t.stride(0), t.stride(1)) if packed else (t.stride(0), t.stride(1), t.stride(2))
+        hf.set(**{f"{name}_ptr": t, f"{name}_batch_stride": st[0], f"{name}_row_stride": st[1], f"{name}_head_stride": st[2]})
+    hf.set(b=b, seqlen_q=msq, seqlen_k=max(lens_k), total_k=tk, h=h, h_k=hk, d=d, dv=d, scale_softmax=1.0 / math.sqrt(d),
+           is_bf16=True, is_causal=True, cu_seqlens_k=cu_k, softmax_lse_ptr=lse, num_sm=148, num_splits=splits,
+           oaccum_ptr=oacc, softmax_lseaccum_ptr=lacc)
+    if varlen_q:
+        hf.set(cu_seqlens_q=cu_q, total_q=tq)
+    if dynamic:
+        hf.set(num_splits_dynamic_ptr=dyn)
+    stream = torch.cuda.current_stream().cuda_stream
+    hf.call("run_mha_fwd", stream)
+    assert capi.last_kernel_kind() == 3, "varlen split decode left the TMA decode kernel"
+    hf.call("run_mha_fwd_combine", stream, False)
+    torch.cuda.synchronize()
+    if dynamic:
+        got = dyn.tolist()
+        assert all(1 <= x <= splits for x in got) and got[0] >= got[2] >= got[1], got     # longer sequences, more splits
+        # surplus splits of short sequences are empty
+        for i in range(b):
+            assert torch.isinf(lacc[got[i]:, i]).all()
+    for i in range(b):
+        rk = slice(int(cu_k[i]), int(cu_k[i + 1]))
+        qi = q[int(cu_q[i]):int(cu_q[i + 1])].unsqueeze(0) if varlen_q else q[i:i + 1]
+        oi = o[int(cu_q[i]):int(cu_q[i + 1])].unsqueeze(0) if varlen_q else o[i:i + 1]
+        sq, sk = qi.shape[1], lens_k[i]
+        mask = orc.causal_mask_bottom_right(sq, sk).to(dev)
+        ref, lse_ref = orc.attention_masked_ref(qi, k[rk].unsqueeze(0), v[rk].unsqueeze(0), mask)
+        pt, _ = orc.attention_masked_ref(qi, k[rk].unsqueeze(0), v[rk].unsqueeze(0), mask, upcast=False, reorder_ops=True)
+        check_2x(f"out[{i}]", oi, ref, pt)
+        got_lse = lse[:, int(cu_q[i]):int(cu_q[i + 1])] if varlen_q else lse[i]
+        torch.testing.assert_close(got_lse.reshape(h, sq), lse_ref[0], atol=2e-3, rtol=1e-3)
+    hf.close()
+
+
+@pytest.mark.gpu
+def test_prepare_num_splits_formula(fa):
+    """fa_b200_prepare_num_splits restates the reference's formula: blocks_per_sm = ceil(1.1 * h_k * sum m_b n_b / num_sm),
+    splits_b = clamp(ceil(n_b / blocks_per_sm), 1, num_splits)."""
+    lib = capi.load()
+    dev = "cuda"
+    used = torch.tensor([32768, 100, 4096, 9000, 1], device=dev, dtype=torch.int32)
+    p = capi.new_params(torch.bfloat16)
+    p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d, p.num_splits = 5, 1, 32768, 32, 8, 128, 16
+    p.seqused_k = used.data_ptr()
+    out = torch.zeros(5, device=dev, dtype=torch.int32)
+    capi.check(lib.fa_b200_prepare_num_splits(p, out.data_ptr(), 148, torch.cuda.current_stream().cuda_stream), "prepare")
+    n = [math.ceil(x / 128) for x in used.tolist()]
+    m = math.ceil(1 * (32 // 8) / 16)
+    bps = max(math.ceil(sum(m * x for x in n) * 1.1 * 8 / 148), 1)
+    want = [max(min(math.ceil(x / bps), 16), 1) for x in n]
+    assert out.tolist() == want, (out.tolist(), want)

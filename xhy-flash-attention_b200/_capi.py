@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
 LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
-FA_B200_ABI_VERSION = 4
+FA_B200_ABI_VERSION = 5
 
 
 class Tensor(C.Structure):
@@ -55,6 +55,7 @@ class Params(C.Structure):
         ("alibi_slopes", C.c_void_p), ("alibi_batch_stride", C.c_int64),
         ("attn_bias", C.c_void_p), ("bias_batch_mod", C.c_int32), ("bias_rows", C.c_int32), ("ds_out", C.c_void_p),
         ("dq_accum_batch_major", C.c_int32), ("seqused_q", C.c_void_p),
+        ("num_splits_dynamic", C.c_void_p),
     ]
 
 
@@ -94,6 +95,8 @@ def load() -> C.CDLL:
     lib.fa_b200_lse_merge_batched.argtypes = ([C.c_void_p] * 4 + [C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int] +
                                               [C.c_int64] * 8 + [C.c_void_p])
     lib.fa_b200_lse_merge_batched.restype = C.c_bool
+    lib.fa_b200_prepare_num_splits.argtypes = [pp, C.c_void_p, C.c_int, C.c_void_p]
+    lib.fa_b200_prepare_num_splits.restype = C.c_bool
     lib.fa_b200_abi_version.restype = C.c_int
     lib.fa_b200_last_kernel_kind.restype = C.c_int
     lib.fa_b200_launch_count.argtypes = [C.c_int]

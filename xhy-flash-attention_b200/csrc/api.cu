@@ -276,6 +276,13 @@ int fa_b200_decode_num_splits(int batch, int num_heads_k, int seqlen_k, int num_
   return best_s;
 }
 
+bool fa_b200_prepare_num_splits(const fa_b200_params *p, int32_t *num_splits_dynamic_out, int num_sm, cudaStream_t stream) {
+  FA_BEGIN
+  FA_CHECK(p && p->abi_version == FA_B200_ABI_VERSION, "fa_b200_params.abi_version mismatch");
+  fa::prepare_num_splits(*p, num_splits_dynamic_out, num_sm, stream);
+  FA_END
+}
+
 bool fa_b200_append_kv(const void *k_new, const void *v_new, void *k_cache, void *v_cache,
                        const int32_t *cache_seqlens, int batch, int seqlen_new, int seqlen_cache,
                        int num_heads_k, int head_size, int is_bf16,

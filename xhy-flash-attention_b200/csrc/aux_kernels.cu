@@ -31,6 +31,11 @@ __global__ void __launch_bounds__(128) combine_kernel(const Params p) {
   const int hq = item % p.h;
   const int row = (item / p.h) % p.seqlen_q;
   const int bi = item / ((int64_t)p.h * p.seqlen_q);
+  // varlen (cu_seqlens_q): the partials are indexed by (batch, row < max_seqlen_q); the output is packed
+  int q_row0, sq_b, k_row0, sk_b;
+  bool q_batched, k_batched;
+  seq_bounds(p, bi, q_row0, sq_b, k_row0, sk_b, q_batched, k_batched);
+  if (row >= sq_b) return;
   const int S = p.num_splits;
   const int64_t lse_split_stride = (int64_t)p.b * p.h * p.seqlen_q;
   const float *lse_in = p.lseaccum + ((int64_t)bi * p.h + hq) * p.seqlen_q + row;
@@ -51,7 +56,8 @@ __global__ void __launch_bounds__(128) combine_kernel(const Params p) {
   const int d = p.d;
   const int64_t o_split_stride = (int64_t)p.b * p.seqlen_q * p.h * d;
   const float *o_in = p.oaccum + (((int64_t)bi * p.seqlen_q + row) * p.h + hq) * (int64_t)d;
-  T *out = (T *)p.o.ptr + bi * p.o.batch_stride + (int64_t)row * p.o.row_stride + (int64_t)hq * p.o.head_stride;
+  T *out = (T *)p.o.ptr + (q_batched ? bi * p.o.batch_stride : 0) + (int64_t)(q_row0 + row) * p.o.row_stride +
+           (int64_t)hq * p.o.head_stride;
   for (int e = lane * 4; e < d; e += 128) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int s = 0; s < S && !empty; ++s) {
@@ -261,6 +267,30 @@ lse_merge_kernel(TO *o, float *lse, const TS *o_step, const float *lse_step, int
   if (lane == 0) lse[li] = ln;
 }
 
+// Per-batch split counts: restates prepare_varlen_num_blocks_kernel (csrc/flash_attn_v3/flash_prepare_scheduler.cu:15-106)
+// with this library's tile sizes (16 packed query rows per m block -- the decode kernel's row tile -- and 128 keys per
+// n block).  One CTA; thread i handles batch element i.
+__global__ void __launch_bounds__(1024) prepare_num_splits_kernel(const Params p, int32_t *out, int num_sm) {
+  __shared__ int total_blocks;
+  if (threadIdx.x == 0) total_blocks = 0;
+  __syncthreads();
+  const int bi = threadIdx.x;
+  int n_blocks = 0, m_blocks = 0;
+  if (bi < p.b) {
+    int q_row0, sq, k_row0, sk;
+    bool qb, kb;
+    seq_bounds(p, bi, q_row0, sq, k_row0, sk, qb, kb);
+    const int leftpad = p.leftpad_k ? p.leftpad_k[bi] : 0;
+    sk = max(min(sk, p.seqlen_k) - leftpad, 0);
+    m_blocks = ceil_div(sq * (p.h / p.h_k), 16);
+    n_blocks = ceil_div(sk, 128);
+    atomicAdd(&total_blocks, m_blocks * n_blocks);
+  }
+  __syncthreads();
+  const int blocks_per_sm = max((int)ceilf((float)total_blocks * 1.1f * (float)p.h_k / (float)num_sm), 1);   // 10% margin
+  if (bi < p.b) out[bi] = max(min(ceil_div(n_blocks, blocks_per_sm), p.num_splits), 1);
+}
+
 __global__ void __launch_bounds__(256) fill_f32_kernel(float *dst, float value, int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) dst[i] = value;
 }
@@ -367,6 +397,14 @@ void lse_merge(void *o, float *lse, const void *o_step, const float *lse_step, i
   if (o_is_fp32) { if (is_bf16) FA_MERGE(float, __nv_bfloat16); else FA_MERGE(float, __half); }
   else { if (is_bf16) FA_MERGE(__nv_bfloat16, __nv_bfloat16); else FA_MERGE(__half, __half); }
 #undef FA_MERGE
+  FA_CUDA(cudaGetLastError());
+  note_launch(1);
+}
+
+void prepare_num_splits(const Params &p, int32_t *out, int num_sm, cudaStream_t s) {
+  FA_CHECK(p.b <= 1024, "prepare_num_splits: batch must be <= 1024");
+  FA_CHECK(out != nullptr && p.num_splits >= 1 && p.h_k > 0, "prepare_num_splits: output and num_splits must be set");
+  prepare_num_splits_kernel<<<1, 1024, 0, s>>>(p, out, num_sm > 0 ? num_sm : device_sm_count());
   FA_CUDA(cudaGetLastError());
   note_launch(1);
 }

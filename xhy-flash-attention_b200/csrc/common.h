@@ -82,6 +82,7 @@ template <typename Kern> inline void ensure_dynamic_smem(Kern kern, int bytes, s
 }
 
 void fill_f32(float *dst, float value, int64_t n, cudaStream_t s);
+void prepare_num_splits(const Params &p, int32_t *out, int num_sm, cudaStream_t s);
 void append_kv_paged(const Params &p, const void *k_new, const void *v_new, int seqlen_new, int64_t nbs, int64_t nrs,
                      int64_t nhs, cudaStream_t s);
 void rotary(const void *x, void *out, const void *cosp, const void *sinp, const int32_t *offsets, int batch, int seqlen,

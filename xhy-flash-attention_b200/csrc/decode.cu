@@ -112,13 +112,19 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   const int n_rt = (p.seqlen_q * (p.h / p.h_k) + kDRows - 1) / kDRows;
   const int split = blockIdx.x / n_rt, rt = blockIdx.x % n_rt, hk = blockIdx.y, bi = blockIdx.z;
   const int g = p.h / p.h_k;
-  const int sq = p.seqlen_q;
+  // lengths and first rows of this batch element (csrc/flashmask_v2/seqlen.h:56-91): cu_seqlens_q / cu_seqlens_k give
+  // packed tensors (no batch dimension), seqused_k a cache length
+  int q_row0, sq, k_row0, sk_all;
+  bool q_batched, k_batched;
+  seq_bounds(p, bi, q_row0, sq, k_row0, sk_all, q_batched, k_batched);
   const int G = sq * g;                                       // packed rows of this (batch, kv-head); this CTA takes
   const int row0 = rt * kDRows;                               // rows [row0, row0 + 16)
   // valid keys are the physical cache rows [leftpad, leftpad + sk) (csrc/flash_attn_v3/seqlen.h:73-80); everything
   // below the mask intervals works on PHYSICAL rows so that 64-key tiles never straddle a page
   const int leftpad = p.leftpad_k ? p.leftpad_k[bi] : 0;
-  const int sk = max((p.seqused_k ? min(p.seqused_k[bi], p.seqlen_k) : p.seqlen_k) - leftpad, 0);
+  const int sk = max(min(sk_all, p.seqlen_k) - leftpad, 0);
+  // splits of this batch element: fixed, or per batch (num_splits_dynamic, flash_prepare_scheduler.cu:15-124)
+  const int nsplit = p.num_splits > 1 ? (p.num_splits_dynamic ? max(min(p.num_splits_dynamic[bi], p.num_splits), 1) : p.num_splits) : 1;
 
   auto full_bar = [&](int s) { return sbase + L::kBar + s * 8; };
   auto empty_bar = [&](int s) { return sbase + L::kBar + (kDStages + s) * 8; };
@@ -132,9 +138,9 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   // key range of this split (same partition as csrc/flashmask_v2/block.h:36-46: whole 128-key blocks per split)
   int split_lo = 0, split_hi = sk;
   if (p.num_splits > 1) {
-    const int per = ceil_div(ceil_div(sk, 128), p.num_splits) * 128;
-    split_lo = split * per;
-    split_hi = min(sk, (split + 1) * per);
+    const int per = ceil_div(ceil_div(sk, 128), nsplit) * 128;
+    split_lo = split < nsplit ? split * per : sk;            // splits beyond this batch element's count are empty
+    split_hi = split < nsplit ? min(sk, (split + 1) * per) : sk;
   }
   int cta_lo = 0x7fffffff, cta_hi = 0;
   for (int qi = row0 / g; qi < sq && qi * g < row0 + kDRows; ++qi) {   // the query rows this row tile touches
@@ -156,7 +162,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
       int page_next = (table && n_tiles > 0) ? table[(t_lo * kDT) / p.page_size] : 0;
       for (int it = 0; it < n_tiles; ++it) {
         const int st = it % kDStages;
-        int row = (t_lo + it) * kDT, slab = bkv;
+        int row = k_row0 + (t_lo + it) * kDT, slab = k_batched ? bkv : 0;
         if (table) {
           slab = page_next;
           row -= (row / p.page_size) * p.page_size;
@@ -180,7 +186,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
   // Q fragments (A operand, 16 packed rows x HD): packed row r -> query index r / g, head hk * g + r % g
   uint32_t qa[HD / 16][4];
   {
-    const T *qb = (const T *)p.q.ptr + (int64_t)bi * p.q.batch_stride;
+    const T *qb = (const T *)p.q.ptr + (q_batched ? (int64_t)bi * p.q.batch_stride : 0) + (int64_t)q_row0 * p.q.row_stride;
     const T *qrowA = rA < G ? qb + (int64_t)(rA / g) * p.q.row_stride + (int64_t)(hk * g + rA % g) * p.q.head_stride : nullptr;
     const T *qrowB = rB < G ? qb + (int64_t)(rB / g) * p.q.row_stride + (int64_t)(hk * g + rB % g) * p.q.head_stride : nullptr;
 #pragma unroll
@@ -349,13 +355,13 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
         acc[i] = a * inv;
       }
       if (p.num_splits > 1) {
-        float *oa = p.oaccum + ((((int64_t)split * p.b + bi) * sq + qi) * p.h + hq) * (int64_t)HD + cg * kPer;
+        float *oa = p.oaccum + ((((int64_t)split * p.b + bi) * p.seqlen_q + qi) * p.h + hq) * (int64_t)HD + cg * kPer;
 #pragma unroll
         for (int i = 0; i < kPer; i += 4) *reinterpret_cast<float4 *>(oa + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
-        if (cg == 0) p.lseaccum[(((int64_t)split * p.b + bi) * p.h + hq) * sq + qi] = lse;
+        if (cg == 0) p.lseaccum[(((int64_t)split * p.b + bi) * p.h + hq) * p.seqlen_q + qi] = lse;
       } else {
-        T *out = (T *)p.o.ptr + (int64_t)bi * p.o.batch_stride + (int64_t)qi * p.o.row_stride + (int64_t)hq * p.o.head_stride +
-                 cg * kPer;
+        T *out = (T *)p.o.ptr + (q_batched ? (int64_t)bi * p.o.batch_stride : 0) + (int64_t)(q_row0 + qi) * p.o.row_stride +
+                 (int64_t)hq * p.o.head_stride + cg * kPer;
 #pragma unroll
         for (int i = 0; i < kPer; i += 8) {
           uint4 v;
@@ -364,7 +370,7 @@ decode_kernel(const __grid_constant__ Params p, const __grid_constant__ DecTma t
           *reinterpret_cast<uint4 *>(out + i) = v;
         }
         if (cg == 0)
-          p.softmax_lse[((int64_t)bi * p.h + hq) * sq + qi] =
+          p.softmax_lse[((int64_t)bi * p.h + hq) * p.seqlen_q + qi] =
               empty ? (p.lse_empty_is_neg_inf ? -CUDART_INF_F : CUDART_INF_F) : lse;
       }
     }
@@ -396,8 +402,9 @@ template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s
   using L = DecSmem<HD>;
   DecTma tm;
   // contiguous cache: (d, h_k, seqlen_k, cache batch); paged: (d, h_k, page_size, num_pages)
-  const int64_t rows = p.page_table ? p.page_size : p.seqlen_k;
-  const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
+  const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
+  const int64_t rows = p.page_table ? p.page_size : (packed_k ? p.total_k : p.seqlen_k);
+  const int slabs = p.page_table ? p.num_pages : packed_k ? 1 : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
   tm.k = make_tma_4d(kv_desc(p.k, p.d, p.h_k, rows, slabs));
   tm.v = make_tma_4d(kv_desc(p.v, p.d, p.h_k, rows, slabs));
   auto kern = decode_kernel<HD, kBf16>;
@@ -415,10 +422,12 @@ template <int HD, bool kBf16> void launch_decode(const Params &p, cudaStream_t s
 bool decode_supported(const Params &p) {
   if (p.force_generic) return false;
   if (p.d != 64 && p.d != 128) return false;
-  if (p.cu_seqlens_q || p.cu_seqlens_k || p.lt_start || p.seqused_q) return false;
+  if (p.lt_start || p.seqused_q) return false;
+  const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
+  if (packed_k && (p.total_k < 0 || p.page_table || p.kv_batch_idx)) return false;   // packed K/V: total rows must be known
   if (p.seqlen_q * (p.h / p.h_k) > kDMaxRows) return false;   // beyond that the tcgen05 forward is the better tool
   if (p.page_table && (p.page_size <= 0 || p.page_size % kDT != 0 || p.num_pages <= 0)) return false;
-  const int slabs = p.page_table ? p.num_pages : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
+  const int slabs = p.page_table ? p.num_pages : packed_k ? 1 : (p.kv_batch_idx && p.b_k > 0 ? p.b_k : p.b);
   if (!kv_ok(p.k, p.h_k, slabs) || !kv_ok(p.v, p.h_k, slabs)) return false;
   if (((uintptr_t)p.q.ptr & 3) != 0 || p.q.row_stride % 2 != 0 || p.q.head_stride % 2 != 0 || p.q.batch_stride % 2 != 0)
     return false;

@@ -35,9 +35,8 @@ fa_b200_tensor tens(void *ptr, int64_t bs, int64_t rs, int64_t hs) {
   return t;
 }
 
-bool decode_shape(const Flash_fwd_params &h) {
-  return h.cu_seqlens_q == nullptr && h.cu_seqlens_k == nullptr && h.lt_start_ptr == nullptr && h.h_k > 0 &&
-         h.seqlen_q * (h.h / h.h_k) <= 128 && (h.d == 64 || h.d == 128);
+bool decode_shape(const Flash_fwd_params &h) {   // seqlen_q is the maximum over the batch when cu_seqlens_q is given
+  return h.lt_start_ptr == nullptr && h.h_k > 0 && h.seqlen_q * (h.h / h.h_k) <= 128 && (h.d == 64 || h.d == 128);
 }
 
 // (h, total_q) <-> (b, h, max_seqlen_q): the v2/v3 surface keeps varlen LSE packed (flash_fwd_launch_template.h:161-164)
@@ -190,26 +189,32 @@ void run_fwd_handle(Flash_fwd_params *hp, cudaStream_t stream) {
     FA_CUDA(cudaFreeAsync(scratch, stream));
     return;
   }
-  if (h.num_splits > 1 || decode_shape(h)) {
-    p.softmax_lse = (float *)h.softmax_lse_ptr;
-    fa::run_splitkv(p, stream);
-    return;
-  }
-  if (h.cu_seqlens_q) {   // varlen: the kernels write (b, h, max_seqlen_q); this surface wants (h, total_q)
+  // varlen: the kernels write LSE as (b, h, max_seqlen_q); this surface wants (h, total_q) (flash_fwd_launch_template.h:161-164)
+  auto run_with_lse = [&](auto &&launch) {
+    if (!h.cu_seqlens_q) { p.softmax_lse = (float *)h.softmax_lse_ptr; launch(); return; }
     require(h.total_q > 0, "total_q must be set with cu_seqlens_q");
     float *tmp = nullptr;
     FA_CUDA(cudaMallocAsync(&tmp, sizeof(float) * (size_t)h.b * h.h * h.seqlen_q, stream));
     p.softmax_lse = tmp;
-    fa::run_fwd(p, stream);
+    try { launch(); } catch (...) { cudaFreeAsync(tmp, stream); throw; }
     dim3 grid(fa::ceil_div(h.seqlen_q, 128), h.h, h.b);
     lse_repack_kernel<<<grid, 128, 0, stream>>>((float *)h.softmax_lse_ptr, tmp, h.cu_seqlens_q, h.b, h.h, h.seqlen_q,
                                                 h.total_q, 1);
     FA_CUDA(cudaGetLastError());
     FA_CUDA(cudaFreeAsync(tmp, stream));
+  };
+  if (h.num_splits > 1 || decode_shape(h)) {
+    if (h.num_splits > 1 && h.num_splits_dynamic_ptr) {
+      // per-batch split counts (csrc/flash_attn_v3/flash.h:96-125): computed here unless the caller says the metadata in
+      // num_splits_dynamic_ptr is already there (skip_scheduler_metadata_computation), then used by the kernel + combine
+      if (!h.skip_scheduler_metadata_computation) fa::prepare_num_splits(p, h.num_splits_dynamic_ptr, h.num_sm, stream);
+      p.num_splits_dynamic = h.num_splits_dynamic_ptr;
+    }
+    if (h.num_splits > 1) { p.softmax_lse = (float *)h.softmax_lse_ptr; fa::run_splitkv(p, stream); }   // partials only
+    else run_with_lse([&] { fa::run_splitkv(p, stream); });
     return;
   }
-  p.softmax_lse = (float *)h.softmax_lse_ptr;
-  fa::run_fwd(p, stream);
+  run_with_lse([&] { fa::run_fwd(p, stream); });
 }
 
 void run_combine_handle(Flash_fwd_params *hp, cudaStream_t stream) {
@@ -218,9 +223,17 @@ void run_combine_handle(Flash_fwd_params *hp, cudaStream_t stream) {
   Params p = common_params(h);
   require(h.num_splits > 1, "run_mha_fwd_combine needs num_splits > 1");
   set_split(p, h);
-  p.softmax_lse = (float *)h.softmax_lse_ptr;
-  require(p.softmax_lse && p.o.ptr, "o_ptr and softmax_lse_ptr must be set");
-  fa::combine_fwd(p, stream);
+  require(h.softmax_lse_ptr && p.o.ptr, "o_ptr and softmax_lse_ptr must be set");
+  if (!h.cu_seqlens_q) { p.softmax_lse = (float *)h.softmax_lse_ptr; fa::combine_fwd(p, stream); return; }
+  require(h.total_q > 0, "total_q must be set with cu_seqlens_q");     // varlen: combine into (b, h, max), repack to (h, total_q)
+  float *tmp = nullptr;
+  FA_CUDA(cudaMallocAsync(&tmp, sizeof(float) * (size_t)h.b * h.h * h.seqlen_q, stream));
+  p.softmax_lse = tmp;
+  try { fa::combine_fwd(p, stream); } catch (...) { cudaFreeAsync(tmp, stream); throw; }
+  dim3 grid(fa::ceil_div(h.seqlen_q, 128), h.h, h.b);
+  lse_repack_kernel<<<grid, 128, 0, stream>>>((float *)h.softmax_lse_ptr, tmp, h.cu_seqlens_q, h.b, h.h, h.seqlen_q, h.total_q, 1);
+  FA_CUDA(cudaGetLastError());
+  FA_CUDA(cudaFreeAsync(tmp, stream));
 }
 
 void run_bwd_handle(Flash_bwd_params *hp, cudaStream_t stream) {

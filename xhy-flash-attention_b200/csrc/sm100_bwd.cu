@@ -23,6 +23,22 @@
 #include "common.h"
 #include "sm100.cuh"
 
+#ifdef FA_TRACE
+// Timeline probe (variant builds only, tools/trace_bwd.py): CTA (0,0,0) records clock64() at the hand-over points of its
+// first iterations -- role 0/1 = compute warpgroup 0/1 (first warp), role 2 = MMA issuer, role 3 = dQ reducer warp 8.
+__device__ unsigned long long fa_trace_bwd_buf[4][96][8];
+#define FB_TR(role, it, ev) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (it) < 96) \
+  fa_trace_bwd_buf[role][it][ev] = clock64(); } while (0)
+extern "C" int fa_b200_trace_bwd_dump(unsigned long long *host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, fa_trace_bwd_buf, sizeof(fa_trace_bwd_buf));
+}
+#define FB_TR_DEP(role, it, ev, val) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (it) < 96) { \
+  unsigned long long t__; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t__) : "r"(val)); fa_trace_bwd_buf[role][it][ev] = t__; } } while (0)
+#else
+#define FB_TR(role, it, ev) do { } while (0)
+#define FB_TR_DEP(role, it, ev, val) do { } while (0)
+#endif
+
 namespace fa {
 namespace {
 
@@ -387,11 +403,14 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
       for (int it = 0; it < n_it_u; ++it) {
         const int st = it & 1;
         const uint32_t sQ = sbase + L::kQ + st * L::kTile;
+        FB_TR(2, it, 0);
         mbar_wait(bar(BB_DO_FULL), it & 1);
         if (it > 0) mbar_wait(bar(BB_DQ_EMPTY), (it - 1) & 1);   // dQ(it-1) has left TMEM: the dP region is free
+        FB_TR(2, it, 1);
         tc_fence_after();
         kmajor_pair(TDP, sV, sDO, bar(BB_DP_FULL));
         mbar_wait(bar(BB_P_FULL), it & 1);
+        FB_TR(2, it, 2);
         tc_fence_after();
         tmem_a_mn_b(TDV, TS_, sDO, it > 0, bar(BB_DO_EMPTY));
         if (it + 1 < n_it_u) {
@@ -399,8 +418,17 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
           tc_fence_after();
           kmajor_pair(TS_, sK, sbase + L::kQ + (st ^ 1) * L::kTile, bar(BB_S_FULL));
         }
+        FB_TR(2, it, 3);
         mbar_wait(bar(BB_DS_FULL), it & 1);
+        FB_TR(2, it, 4);
         tc_fence_after();
+        // dK reads dS^T (packed 16-bit) from the dP/dS/dQ TMEM region and dQ overwrites that region: dK first on the
+        // in-order pipe.  Tried in round 2 (timeline probe: the cycle dS ready -> dK -> dQ -> reducers drain dQ -> dP of the
+        // next block -> dS phase is the critical one): dQ first with dK reading dS^T from SHARED memory instead, so that dK
+        // runs while the reducers drain.  Correct, but 7.5 % SLOWER on C3 (1180 -> 1092 TFLOPS): an SS MMA of this shape is
+        // shared-memory-bandwidth bound (tools/tmem_bench.cu: 675 cycles per 128^3 against 544 for TS), and the block's
+        // MMA stream -- S, dP, dQ in SS mode, dV, dK in TS mode: 3 x 675 + 2 x 544 = 3113 cycles -- is already 84 % of the
+        // measured 3700-cycle period.  What would help is cta_group::2 (a CTA pair shares the B operand), not reordering.
         tmem_a_mn_b(TDK, TDP, sQ, it > 0, bar(BB_Q_EMPTY + st));
         if (elect_one()) {
 #pragma unroll
@@ -432,7 +460,9 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
       const int hq = cur.hq, m = cur.m;
       const int64_t tile_idx = acc_tile_index(p, t, hq, m);
       float *gtile = p.dq_accum + tile_idx * (int64_t)(p.d_rounded / 32) * (kB * 32);
+      if (warp == 8) FB_TR(3, it, 0);
       mbar_wait(bar(BB_DQ_FULL), it & 1);
+      if (warp == 8) FB_TR(3, it, 1);
       tc_fence_after();
       uint32_t v[HD / 32][32];
 #pragma unroll
@@ -441,6 +471,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(bar(BB_DQ_EMPTY));
+      if (warp == 8) FB_TR(3, it, 2);
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
         if (c < n_chunks) {
@@ -558,8 +589,10 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
           }
         }
       }
+      if (warp % 4 == 0) FB_TR(wg, it, 0);
       mbar_wait(bar(BB_Q_FULL + st), (it >> 1) & 1);   // LSE / dPsum rows of this query block are in smem
       mbar_wait(bar(BB_S_FULL), it & 1);
+      if (warp % 4 == 0) FB_TR(wg, it, 1);
       tc_fence_after();
       float pr[64];
 #pragma unroll
@@ -621,20 +654,24 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
 #pragma unroll
           for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[c2 * 32 + 2 * i], pr[c2 * 32 + 2 * i + 1]);
         }
+        if (warp % 4 == 0 && c2 == 1) FB_TR_DEP(wg, it, 5, pk[15]);
         tmem_st16(tP + c2 * 16, pk);
       }
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(bar(BB_P_FULL));
+      if (warp % 4 == 0) FB_TR(wg, it, 2);
 
       mbar_wait(bar(BB_DP_FULL), it & 1);
       if (it > 0) mbar_wait(bar(BB_DQ_FULL), (it - 1) & 1);  // dQ(it-1) no longer reads the dS^T smem tile
+      if (warp % 4 == 0) FB_TR(wg, it, 3);
       tc_fence_after();
 #pragma unroll
       for (int c2 = 0; c2 < 2; ++c2) {
         uint32_t dp[32];
         tmem_ld32(tDP + c2 * 32, dp);
         tmem_wait_ld();
+        if (warp % 4 == 0 && c2 == 1) FB_TR_DEP(wg, it, 6, dp[31]);
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
@@ -670,9 +707,11 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
           sts128(ds_row_a + (((c2 * 4 + j) ^ (r & 7)) * 16), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
       }
       tmem_wait_st();
+      if (warp % 4 == 0) FB_TR(wg, it, 7);
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bar(BB_DS_FULL));
+      if (warp % 4 == 0) FB_TR(wg, it, 4);
     }
     // ---------------- epilogue: dK (x scale), dV ----------------
     const bool row_ok = col < t.sk;
