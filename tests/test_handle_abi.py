@@ -397,7 +397,7 @@ def test_handle_varlen_split_decode(fa, varlen_q, dynamic):
         assert all(1 <= x <= splits for x in got) and got[0] >= got[2] >= got[1], got     # longer sequences, more splits
         # surplus splits of short sequences are empty
         for i in range(b):
-            assert torch.isinf(lacc[got[i]:, i]).all()
+            assert torch.isinf(lacc[got[i]:, i, :, :lens_q[i]]).all()
     for i in range(b):
         rk = slice(int(cu_k[i]), int(cu_k[i + 1]))
         qi = q[int(cu_q[i]):int(cu_q[i + 1])].unsqueeze(0) if varlen_q else q[i:i + 1]
