@@ -43,8 +43,10 @@ def flashmask_args(fm, b, sk, device):
     return args, (dims, ws)
 
 
-def flat_fwd(lib, q, k, v, causal, scale=None, fm=None, attn_mask=None, err=None):
-    """flash_attn_fwd on (b, s, h, d) tensors.  Returns (out, lse)."""
+def flat_fwd(lib, q, k, v, causal, scale=None, fm=None, attn_mask=None, err=None, p_dropout=0.0, return_softmax=False,
+             seed=0, offset=0):
+    """flash_attn_fwd on (b, s, h, d) tensors.  Returns (out, lse), or (out, lse, S_dmask) with return_softmax --
+    S_dmask (b, h, sq_rounded, sk_rounded) in the element type, csrc/flash_attn/flash_api.cpp:276-279."""
     b, sq, h, d = q.shape
     sk, hk = k.shape[1], k.shape[2]
     scale = d ** -0.5 if scale is None else scale
@@ -57,18 +59,19 @@ def flat_fwd(lib, q, k, v, causal, scale=None, fm=None, attn_mask=None, err=None
     # the reference's forward kernel stores (seed, offset) into rng_state UNCONDITIONALLY (flash_fwd_kernel.h:320-324),
     # dropout or not: a caller must always pass two uint64 of device memory
     rng_state = torch.zeros(2, dtype=torch.int64, device=q.device)
+    S = torch.full((b, h, round_up(sq, 128), round_up(sk, 128)), float("nan"), device=q.device, dtype=q.dtype) if return_softmax else None
     lib.flash_attn_fwd.restype = C.c_bool
     ok = lib.flash_attn_fwd(
-        _vp(q), _vp(k), _vp(v), _vp(rng_state), _vp(out), None, _vp(lse), C.c_int(b), C.c_int(sq), C.c_int(sk),
+        _vp(q), _vp(k), _vp(v), _vp(rng_state), _vp(out), _vp(S), _vp(lse), C.c_int(b), C.c_int(sq), C.c_int(sk),
         C.c_int(round_up(sq, 128)), C.c_int(round_up(sk, 128)), C.c_int(h), C.c_int(hk), C.c_int(d),
-        C.c_int(round_up(d, 32)), C.c_float(0.0), C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal),
-        C.c_bool(False), C.c_bool(q.dtype == torch.bfloat16), stream, C.c_uint64(0), C.c_uint64(0),
+        C.c_int(round_up(d, 32)), C.c_float(p_dropout), C.c_float(scale), C.c_float(1.0 / scale), C.c_bool(causal),
+        C.c_bool(return_softmax), C.c_bool(q.dtype == torch.bfloat16), stream, C.c_uint64(seed), C.c_uint64(offset),
         _vp(attn_mask), mask_dims, *fm_args, qr, kr, vr, qh, kh, vh, or_, oh, qb, kb, vb, ob)
     if not ok:
         lib.flash_attn_error.restype = C.c_char_p
         raise RuntimeError((lib.flash_attn_error() or b"").decode())
     del keep
-    return out, lse
+    return (out, lse, S) if return_softmax else (out, lse)
 
 
 def flat_bwd(lib, g, q, k, v, out, lse, causal, scale=None, fm=None, num_splits=0):

@@ -158,3 +158,103 @@ def test_dropout_tcgen05_varlen_and_flashmask(fa, capi):
         res.append((o,) + torch.autograd.grad(o, (q, k, v), g))
     for name, a_, b_ in zip(("out", "dq", "dk", "dv"), res[0], res[1]):
         torch.testing.assert_close(a_.float(), b_.float(), atol=3e-2, rtol=3e-2, msg=lambda m: f"{name}: {m}")
+
+
+def _probs_ref(q, k, causal, fm_dense=None):
+    """fp32 softmax(scale * q k^T) over (b, h, sq, sk) with the top-left causal rule; fully masked rows -> 0."""
+    b, sq, h, d = q.shape
+    sk, hk = k.shape[1], k.shape[2]
+    kk = k.float().repeat_interleave(h // hk, dim=2)
+    s = torch.einsum("bqhd,bkhd->bhqk", q.float(), kk) * d ** -0.5
+    if causal:
+        s = s.masked_fill(orc.causal_mask_top_left(sq, sk).to(q.device), float("-inf"))
+    if fm_dense is not None:
+        s = s.masked_fill(fm_dense, float("-inf"))
+    return torch.nan_to_num(torch.softmax(s, dim=-1), nan=0.0)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("sq,sk,d,h,hk", [(128, 128, 64, 4, 4), (113, 203, 128, 6, 2), (384, 1000, 96, 4, 1), (515, 300, 40, 2, 2),
+                                          (256, 256, 192, 4, 2), (200, 333, 256, 2, 1)])
+def test_s_dmask_tcgen05_pass(fa, capi, sq, sk, d, h, hk, causal, dtype):
+    """return_softmax through the flat C ABI, with and without dropout: the forward stays on the tcgen05 kernels and the
+    S_dmask pass (sm100_probs.cu) gives the normalised probabilities, zeros at masked / padded positions, negative where
+    the weight was dropped -- and the dropped set is exactly the one the generic kernels derive from the same seed."""
+    from tests._flat_capi import flat_fwd
+    lib = capi.load()
+    torch.manual_seed(5)
+    b = 2
+    q = torch.randn(b, sq, h, d, device=DEV, dtype=dtype)
+    k = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype)
+    v = torch.randn(b, sk, hk, d, device=DEV, dtype=dtype)
+    ref = _probs_ref(q, k, causal)
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    n0 = capi.fallback_count()
+    out0, lse0, S0 = flat_fwd(lib, q, k, v, causal, return_softmax=True)
+    assert capi.last_kernel_kind() == 2 and capi.fallback_count() == n0, capi.last_fallback_reason()
+    assert not torch.isnan(S0[:, :, :sq]).any()                      # every column of every real row is written
+    assert (S0[:, :, :sq, sk:] == 0).all()
+    assert (S0[:, :, :sq, :sk].float() - ref).abs().max().item() <= tol
+    out1, lse1 = flat_fwd(lib, q, k, v, causal)
+    assert torch.equal(out0, out1) and torch.equal(lse0, lse1)
+    if d > 128:
+        return                                                         # dropout with head dims > 128 is a generic-kernel call
+    p = 0.17
+    out_d, lse_d, S = flat_fwd(lib, q, k, v, causal, return_softmax=True, p_dropout=p, seed=1234, offset=8)
+    assert capi.last_kernel_kind() == 2 and capi.fallback_count() == n0, capi.last_fallback_reason()
+    S = S[:, :, :sq, :sk].float()
+    assert (S.abs() - ref).abs().max().item() <= tol
+    nz = ref > 1e-4
+    frac = ((S < 0) & nz).float().sum().item() / nz.float().sum().item()
+    assert abs(frac - p) < 0.015, frac
+    # the generic kernels with the same seed (Python surface, seed drawn from torch's generator): same dropped set,
+    # same values up to rounding, same output
+    torch.manual_seed(7)
+    out_f, _, S_f = fa.flash_attn_func(q, k, v, p, None, causal, True)
+    assert capi.last_kernel_kind() == 2 and capi.fallback_count() == n0, capi.last_fallback_reason()
+    torch.manual_seed(7)
+    out_g, _, S_g = fa.flash_attn_func(q, k, v, p, None, causal, True, _force_generic=True)
+    assert capi.last_kernel_kind() == 1
+    S_f, S_g = S_f[:, :, :sq, :sk].float(), S_g[:, :, :sq, :sk].float()
+    assert torch.equal((S_f < 0) & nz, (S_g < 0) & nz)
+    assert (S_f - S_g).abs().max().item() <= tol
+    torch.testing.assert_close(out_f.float(), out_g.float(), atol=2e-2, rtol=2e-2)
+
+
+def test_s_dmask_tcgen05_varlen_flashmask(fa, capi):
+    """The S_dmask pass on a packed batch (per-sequence bounds) and under FlashMask vectors (element-wise rule)."""
+    torch.manual_seed(3)
+    lens, h, d, p = [77, 200, 130], 4, 64, 0.25
+    total = sum(lens)
+    qkv = torch.randn(total, 3, h, d, device=DEV, dtype=torch.bfloat16)
+    cu = torch.tensor([0, 77, 277, 407], device=DEV, dtype=torch.int32)
+    n0 = capi.fallback_count()
+    torch.manual_seed(11)
+    out, lse, S = fa.flash_attn_varlen_qkvpacked_func(qkv, cu, max(lens), p, None, True, True)
+    assert capi.last_kernel_kind() == 2 and capi.fallback_count() == n0, capi.last_fallback_reason()
+    torch.manual_seed(11)
+    out_g, _, S_g = fa.flash_attn_varlen_qkvpacked_func(qkv, cu, max(lens), p, None, True, True, _force_generic=True)
+    for i, n in enumerate(lens):
+        a, e = int(cu[i]), int(cu[i + 1])
+        ref = _probs_ref(qkv[a:e, 0].unsqueeze(0), qkv[a:e, 1].unsqueeze(0), True)
+        Si, Sgi = S[i:i + 1, :, :n, :n].float(), S_g[i:i + 1, :, :n, :n].float()
+        assert (Si.abs() - ref).abs().max().item() <= 2e-2
+        assert torch.equal((Si < 0) & (ref > 1e-4), (Sgi < 0) & (ref > 1e-4))
+        assert (S[i, :, :n, n:] == 0).all()
+    torch.testing.assert_close(out.float(), out_g.float(), atol=2e-2, rtol=2e-2)
+    # FlashMask (document mask: LT start = end of the column's document), dense
+    b, s = 2, 384
+    q, k, v = [torch.randn(b, s, h, d, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    doc_end = torch.tensor([100, 100 + 150, s], device=DEV)
+    col = torch.arange(s, device=DEV)
+    lts = doc_end[torch.bucketize(col, doc_end, right=True)].to(torch.int32).view(1, 1, s).expand(b, 1, s).contiguous()
+    torch.manual_seed(13)
+    out, lse, S = fa.flash_attn_func(q, k, v, p, None, True, True, flashmask=(lts, None, None, None))
+    assert capi.last_kernel_kind() == 2 and capi.fallback_count() == n0, capi.last_fallback_reason()
+    row = torch.arange(s, device=DEV).view(s, 1)
+    dense = (row >= lts[0, 0].view(1, s)).view(1, 1, s, s)
+    ref = _probs_ref(q, k, True, dense)
+    Sf = S[:, :, :s, :s].float()
+    assert (Sf.abs() - ref).abs().max().item() <= 2e-2
+    assert (Sf[dense.expand_as(Sf)] == 0).all()

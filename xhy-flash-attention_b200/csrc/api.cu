@@ -107,15 +107,31 @@ void run_fwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
-  // return_softmax needs the element-wise generic pass; so do softcap / ALiBi and the KV-cache addressing modes outside
-  // the decode kernel (inference features).  Dropout, the dense attn_mask and softcap have tcgen05 instantiations.
-  const char *special = p.s_dmask != nullptr ? "return_softmax (S_dmask)"
+  if (p.force_generic) { generic_fwd(p, s); return; }      // asked for by the caller (tests, FA1 symbols): not a fallback
+  // return_softmax: out and LSE come from the same tcgen05 kernels as without it, then one more tcgen05 pass writes
+  // S_dmask from Q, K and the finished LSE (sm100_probs.cu).  Only logits that are more than scale * q.k (dense mask,
+  // softcap, ALiBi, FA1 bias) keep the element-wise generic pass for it.
+  if (p.s_dmask != nullptr && sm100_probs_eligible(p)) {
+    Params main_pass = p;
+    main_pass.s_dmask = nullptr;
+    if (sm100_fwd_supported(main_pass, &why)) {
+      tls_fallback_reason.clear();
+      sm100_fwd(main_pass, s);
+      sm100_probs(p, s);
+      return;
+    }
+    note_fallback("forward", why);
+    generic_fwd(p, s);
+    return;
+  }
+  // ALiBi and the KV-cache addressing modes outside the decode kernel (inference features) run on the generic kernels.
+  // Dropout, the dense attn_mask and softcap have tcgen05 instantiations.
+  const char *special = p.s_dmask != nullptr ? "return_softmax (S_dmask) with a dense mask / softcap / ALiBi / bias"
                         : p.alibi_slopes != nullptr ? "alibi_slopes outside the decode kernel"
                         : p.page_table != nullptr ? "paged KV outside the decode kernel"
                         : p.kv_batch_idx != nullptr ? "kv_batch_idx outside the decode kernel"
                         : p.leftpad_k != nullptr ? "leftpad_k outside the decode kernel"
                         : p.attn_bias != nullptr ? "attn_bias (FA1 bias path)" : nullptr;
-  if (p.force_generic) { generic_fwd(p, s); return; }      // asked for by the caller (tests, FA1 symbols): not a fallback
   if (special) why = special;
   if (!special && sm100_fwd_supported(p, &why)) { tls_fallback_reason.clear(); sm100_fwd(p, s); return; }
   note_fallback("forward", why);

@@ -15,12 +15,14 @@ Behaviour kept from the reference:
   * causal masks are TOP-LEFT aligned                                            (tests/test_flash_attn.py:144-146)
   * packed inputs get one packed gradient tensor                                (:108-113,167-176)
 
-Dropout (``dropout_p > 0``) and ``return_attn_probs`` (``S_dmask``) are served by the generic SIMT kernels with a
-Philox-4x32-10 mask and the reference's 8-bit keep threshold (csrc/flash_attn/src/softmax.h:381-447); the random stream
-is this library's own (one Philox call per 16 columns of a row), so masks are reproducible from ``rng_state`` but not
-bit-identical to the reference's -- the reference's tests check dropout through ``S_dmask`` and the drop fraction,
-which is how tests/test_dropout_gpu.py checks it here.  ``S_dmask`` is plain row-major
-(batch, heads, seqlen_q_rounded, seqlen_k_rounded): softmax probabilities, negated where dropped.
+Dropout (``dropout_p > 0``) runs inside the tcgen05 forward / backward kernels for head dims up to 128 (generic SIMT
+kernels beyond) with a Philox-4x32-10 mask and the reference's 8-bit keep threshold
+(csrc/flash_attn/src/softmax.h:381-447); the random stream is this library's own (one Philox call per 16 columns of a
+row), so masks are reproducible from ``rng_state`` but not bit-identical to the reference's -- the reference's tests
+check dropout through ``S_dmask`` and the drop fraction, which is how tests/test_dropout_gpu.py checks it here.
+``return_attn_probs`` keeps the forward on the same kernels and adds one tcgen05 pass (csrc/sm100_probs.cu) that writes
+``S_dmask`` from Q, K and the finished LSE: plain row-major (batch, heads, seqlen_q_rounded, seqlen_k_rounded), softmax
+probabilities, negated where dropped, zero where masked.
 
 Added on top of the reference surface (keyword-only, all default to the reference behaviour):
 ``window_size``, ``flashmask`` (the fork's column-sparse mask vectors), ``flash_attn_with_kvcache``
