@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 5
+#define FA_B200_ABI_VERSION 6
 
 /* One strided (batch, row, head, d) view; strides in ELEMENTS, innermost stride 1.
  * For packed varlen tensors batch_stride is ignored (rows are indexed through cu_seqlens). */
@@ -128,6 +128,15 @@ typedef struct fa_b200_params {
   const int32_t *num_splits_dynamic; /* (b) int32 or NULL: batch element i is cut into num_splits_dynamic[i] <= num_splits
                                         key ranges; the partial results of the remaining splits are written as empty
                                         (lse = -inf) and the combine skips them.  fa_b200_prepare_num_splits fills it. */
+  /* ---- FP8 forward (ABI v6; reference: is_e4m3 + *_descale_ptr, csrc/flashmask_v2/flash.h:55-63,144 and
+   *      flash_api.cu:107-131) ---- */
+  int32_t is_e4m3;                /* 1 = q, k, v hold e4m3 bytes (strides in elements = bytes); out is bf16; forward only */
+  const float *q_descale;         /* per (batch, kv head) fp32 factors or NULL (= 1): logits are scaled by            */
+  const float *k_descale;         /*   q_descale * k_descale (mainloop_fwd_sm90_tma_gmma_ws.hpp:1612-1614), out by    */
+  const float *v_descale;         /*   v_descale (:1868-1869)                                                         */
+  int64_t q_descale_batch_stride, q_descale_head_stride;
+  int64_t k_descale_batch_stride, k_descale_head_stride;
+  int64_t v_descale_batch_stride, v_descale_head_stride;
 } fa_b200_params;
 
 /* forward: O, LSE.  Equivalent of {flashmaskv2,fa3}_run_mha_fwd (csrc/flashmask_v2/flash_api.h). */

@@ -19,8 +19,9 @@
  * (+ b_k), leftpad_k, knew / vnew (appended at seqused_k, then attended), rotary_cos / rotary_sin (+ rotary_dim,
  * is_rotary_interleaved; applied to q and knew), softcap (forward and backward).
  * seqused_q limits the query rows of each batch element (forward and backward).
- * Fields accepted but requiring an unsupported feature make run_* throw: fp8 (is_e4m3), qv, cu_seqlens_knew,
- * p_dropout < 1, dv != d.
+ * is_e4m3 (+ q/k/v_descale_ptr and their strides): FP8 forward, e4m3 q/k/v bytes in, bf16 out (flash_api.cu:107-131);
+ * plain / causal / local / varlen calls, head dim a multiple of 16; anything else with is_e4m3 throws.
+ * Fields accepted but requiring an unsupported feature make run_* throw: qv, cu_seqlens_knew, p_dropout < 1, dv != d.
  */
 #ifndef FA_B200_HANDLE_H_
 #define FA_B200_HANDLE_H_

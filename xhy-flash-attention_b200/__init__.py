@@ -11,6 +11,7 @@ from .host_pipeline import HostPipeline  # noqa: F401
 from . import bert_padding  # noqa: F401
 from .varlen_shard import VarlenShard, flash_attn_varlen_sharded, lpt_assign, shard_varlen  # noqa: F401
 from .flash_attn_interface import (  # noqa: F401
+    flash_attn_fp8_func,
     flash_attn_func,
     flash_attn_kvpacked_func,
     flash_attn_qkvpacked_func,

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # FA_B200_LIB: load another build of the same library (A/B timing of two builds on one box); default = the in-tree build
 LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "lib", "libflashattn_b200.so")
 
-FA_B200_ABI_VERSION = 5
+FA_B200_ABI_VERSION = 6
 
 
 class Tensor(C.Structure):
@@ -56,6 +56,10 @@ class Params(C.Structure):
         ("attn_bias", C.c_void_p), ("bias_batch_mod", C.c_int32), ("bias_rows", C.c_int32), ("ds_out", C.c_void_p),
         ("dq_accum_batch_major", C.c_int32), ("seqused_q", C.c_void_p),
         ("num_splits_dynamic", C.c_void_p),
+        ("is_e4m3", C.c_int32), ("q_descale", C.c_void_p), ("k_descale", C.c_void_p), ("v_descale", C.c_void_p),
+        ("q_descale_batch_stride", C.c_int64), ("q_descale_head_stride", C.c_int64),
+        ("k_descale_batch_stride", C.c_int64), ("k_descale_head_stride", C.c_int64),
+        ("v_descale_batch_stride", C.c_int64), ("v_descale_head_stride", C.c_int64),
     ]
 
 

@@ -107,6 +107,17 @@ void run_fwd(const Params &p, cudaStream_t s) {
   FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
+  if (p.is_e4m3) {
+    // FP8 forward (csrc/flashmask_v2/flash_api.cu:107-131): tensor-core kernel or nothing -- there is no byte-operand
+    // generic kernel to fall back to
+    FA_CHECK(!p.force_generic && p.s_dmask == nullptr && p.alibi_slopes == nullptr && p.page_table == nullptr &&
+             p.kv_batch_idx == nullptr && p.leftpad_k == nullptr && p.attn_bias == nullptr,
+             "FP8 forward: plain / causal / local / varlen calls only");
+    if (!sm100_fwd_supported(p, &why)) throw Error("FP8 forward: " + why);
+    tls_fallback_reason.clear();
+    sm100_fwd(p, s);
+    return;
+  }
   if (p.force_generic) { generic_fwd(p, s); return; }      // asked for by the caller (tests, FA1 symbols): not a fallback
   // return_softmax: out and LSE come from the same tcgen05 kernels as without it, then one more tcgen05 pass writes
   // S_dmask from Q, K and the finished LSE (sm100_probs.cu).  Only logits that are more than scale * q.k (dense mask,
@@ -142,6 +153,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
   check_common(p);
   FA_CHECK(p.o.ptr && p.softmax_lse && p.dout.ptr && p.dq.ptr && p.dk.ptr && p.dv.ptr, "bwd tensors must be set");
   FA_CHECK(p.softmax_d, "softmax_d workspace must be set");
+  FA_CHECK(!p.is_e4m3, "FP8 is forward-only (as in the reference: csrc/flashmask_v2/flash_api.cu:107-131 has no e4m3 backward)");
   std::string why;
   FA_CHECK(p.p_dropout >= 0.f && p.p_dropout < 1.f, "p_dropout must be in [0, 1)");
   FA_CHECK(!p.page_table && !p.kv_batch_idx && !p.leftpad_k, "backward: KV-cache addressing (page_table / kv_batch_idx / leftpad_k) is forward-only");
@@ -156,6 +168,7 @@ void run_bwd(const Params &p, cudaStream_t s) {
 
 void run_splitkv(const Params &p, cudaStream_t s) {
   check_common(p);
+  FA_CHECK(!p.is_e4m3, "FP8 split-KV is not supported");
   if (p.num_splits > 1) FA_CHECK(p.oaccum && p.lseaccum, "split-KV needs oaccum and lseaccum");
   else FA_CHECK(p.o.ptr && p.softmax_lse, "out and softmax_lse must be set");
   splitkv_fwd(p, s);

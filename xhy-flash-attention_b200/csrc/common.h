@@ -57,6 +57,7 @@ bool sm100_fwd_supported(const Params &p, std::string *why);
 void sm100_fwd(const Params &p, cudaStream_t s);
 bool sm100_fwd2_eligible(const Params &p);     // split-row forward (sm100_fwd2.cu): plain calls, head dims up to 256
 void sm100_fwd2(const Params &p, cudaStream_t s);
+void sm100_fwd2_e4m3(const Params &p, cudaStream_t s);   // FP8 forward: e4m3 q/k/v, bf16 out (same kernel, byte operands)
 bool sm100_probs_eligible(const Params &p);    // return_softmax pass (sm100_probs.cu): S_dmask from Q, K and the LSE
 void sm100_probs(const Params &p, cudaStream_t s);
 bool sm100_bwd_supported(const Params &p, std::string *why);

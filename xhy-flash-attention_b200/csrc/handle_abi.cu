@@ -52,7 +52,7 @@ __global__ void lse_repack_kernel(float *packed, float *padded, const int *cu, i
 }
 
 Params common_params(const Flash_fwd_params &h) {
-  require(!h.is_e4m3 && !h.is_fp32, "only fp16 / bf16 inputs are supported");
+  require(!h.is_fp32, "fp32 inputs are not supported");
   require(h.softcap >= 0.f, "softcap must be >= 0");
   require(h.qv_ptr == nullptr, "qv is not supported");
   require(h.cu_seqlens_knew == nullptr, "cu_seqlens_knew is not supported");
@@ -64,7 +64,14 @@ Params common_params(const Flash_fwd_params &h) {
   Params p;
   memset(&p, 0, sizeof(p));
   p.abi_version = FA_B200_ABI_VERSION;
-  p.is_bf16 = h.is_bf16 ? 1 : 0;
+  p.is_bf16 = (h.is_bf16 || h.is_e4m3) ? 1 : 0;         // e4m3 inputs: out is bf16 (flash_api.cu: out_type of the FP8 path)
+  if (h.is_e4m3) {
+    p.is_e4m3 = 1;
+    p.q_descale = h.q_descale_ptr; p.k_descale = h.k_descale_ptr; p.v_descale = h.v_descale_ptr;
+    p.q_descale_batch_stride = h.q_descale_batch_stride; p.q_descale_head_stride = h.q_descale_head_stride;
+    p.k_descale_batch_stride = h.k_descale_batch_stride; p.k_descale_head_stride = h.k_descale_head_stride;
+    p.v_descale_batch_stride = h.v_descale_batch_stride; p.v_descale_head_stride = h.v_descale_head_stride;
+  }
   p.q = tens(h.q_ptr, h.q_batch_stride, h.q_row_stride, h.q_head_stride);
   p.k = tens(h.k_ptr, h.k_batch_stride, h.k_row_stride, h.k_head_stride);
   p.v = tens(h.v_ptr, h.v_batch_stride, h.v_row_stride, h.v_head_stride);

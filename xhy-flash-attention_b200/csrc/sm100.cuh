@@ -153,6 +153,38 @@ __device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64
       : "memory");
 }
 
+// The same two forms for 8-bit floating point operands (kind::f8f6f4, K = 32 per instruction; e4m3 here)
+__device__ __forceinline__ void umma_ss_f8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_ts_f8(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// kind::f8f6f4 descriptor, both operands e4m3 (a_format = b_format = 0), fp32 accumulate; MN-major B is legal for 8-bit types
+__host__ __device__ constexpr uint32_t make_idesc_e4m3(int M, int N, bool b_mn_major) {
+  return (1u << 4) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// four fp32 -> four e4m3 in one 32-bit word, element 0 in the low byte (round to nearest, saturating at +-448)
+__device__ __forceinline__ uint32_t pack4_e4m3(float a, float b, float c, float d) {
+  uint32_t r;
+  asm("{\n\t.reg .b16 lo, hi;\n\t"
+      "cvt.rn.satfinite.e4m3x2.f32 lo, %2, %1;\n\t"
+      "cvt.rn.satfinite.e4m3x2.f32 hi, %4, %3;\n\t"
+      "mov.b32 %0, {lo, hi};\n\t}"
+      : "=r"(r) : "f"(a), "f"(b), "f"(c), "f"(d));
+  return r;
+}
+
 // Instruction descriptor for kind::f16, fp32 accumulate (bit layout: cute/arch/mma_sm100_desc.hpp InstrDescriptor):
 //   [4,6) c_format = 1 (F32); [7,10) a_format, [10,13) b_format (0 = F16, 1 = BF16); [15] a_major, [16] b_major
 //   (0 = K-major, 1 = MN-major); [17,23) N >> 3; [24,29) M >> 4.
@@ -170,8 +202,6 @@ __device__ __forceinline__ uint64_t make_sdesc_sw128(uint32_t smem_addr, uint32_
 }
 
 // ---------------------------------------------------------------- TMEM <-> registers (32 lanes x 32-bit, N columns)
-#define FA_R8(a, o) "%" #o ", %" #o "+1"  // (unused helper, kept trivial)
-
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -229,8 +259,9 @@ struct TmaDesc4 {
   uint64_t dims[4];      // elements, innermost first
   uint64_t strides[3];   // bytes, for dims 1..3
   uint32_t box[4];
+  int elem_bytes = 2;    // 2: 16-bit elements; 1: bytes (e4m3)
 };
-// Encodes a 4-D tiled tensor map of 16-bit elements with 128-byte swizzle. Throws fa::Error on failure.
+// Encodes a 4-D tiled tensor map of 16-bit (or 8-bit) elements with 128-byte swizzle. Throws fa::Error on failure.
 CUtensorMap make_tma_4d(const TmaDesc4 &d);
 // Copies n (<= 4) host-encoded maps to a stream-ordered device allocation and patches dimension 2 (rows) of map i to
 // cu_seqlens_k[b] (k_like[i] != 0) or cu_seqlens_q[b] ON THE DEVICE (tma_host.cu).  cudaFreeAsync the result.

@@ -1104,6 +1104,24 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCa
 
 bool sm100_fwd_supported(const Params &p, std::string *why) {
   auto no = [&](const char *w) { if (why) *why = w; return false; };
+  if (p.is_e4m3) {
+    // FP8 forward (sm100_fwd2.cu, byte operands): strides are in bytes, TMA wants multiples of 16
+    if (!sm100_fwd2_eligible(p)) return no("FP8 together with FlashMask / dropout / attn_mask / softcap");
+    if (p.num_splits > 1) return no("FP8 split-KV");
+    if (p.d % 16 != 0) return no("FP8 needs head_size % 16 == 0");
+    if ((bool)p.cu_seqlens_q != (bool)p.cu_seqlens_k) return no("cu_seqlens_q and cu_seqlens_k go together");
+    const bool pk = p.cu_seqlens_q && !p.varlen_padded_input;
+    auto ok8 = [&](const fa_b200_tensor &t, int heads, int batch) {
+      return ((uintptr_t)t.ptr & 15) == 0 && t.row_stride > 0 && t.row_stride % 16 == 0 &&
+             (heads <= 1 || (t.head_stride > 0 && t.head_stride % 16 == 0)) &&
+             (batch <= 1 || (t.batch_stride > 0 && t.batch_stride % 16 == 0));
+    };
+    if (!ok8(p.q, p.h, pk ? 1 : p.b) || !ok8(p.k, p.h_k, pk ? 1 : p.b) || !ok8(p.v, p.h_k, pk ? 1 : p.b))
+      return no("FP8 strides/alignment not TMA-compatible");
+    if (((uintptr_t)p.o.ptr & 15) != 0 || p.o.row_stride % 8 != 0 || p.o.head_stride % 8 != 0 || p.o.batch_stride % 8 != 0)
+      return no("output not 16-byte aligned");
+    return true;
+  }
   if (p.d > 128 && !sm100_fwd2_eligible(p)) return no("head_size > 128 together with FlashMask / dropout / attn_mask / softcap");
   if (p.num_splits > 1) return no("split-KV");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f)) return no("dense attn_mask together with FlashMask / dropout");
@@ -1137,6 +1155,7 @@ void sm100_fwd(const Params &p, cudaStream_t s) {
   // kernel below is faster (measured on C3: 1123 vs 1028 TFLOPS with two Q tiles per CTA, 1081 with one);
   // FA_B200_FWD2=1 selects the split-row kernel there too (A/B measurements)
   static const bool use_fwd2 = [] { const char *e = getenv("FA_B200_FWD2"); return e && e[0] == '1'; }();
+  if (p.is_e4m3) { sm100_fwd2_e4m3(p, s); return; }
   if (sm100_fwd2_eligible(p) && (p.d > 128 || use_fwd2)) { sm100_fwd2(p, s); return; }
   if (p.d <= 64) { if (p.is_bf16) dispatch_fwd<64, true>(p, s); else dispatch_fwd<64, false>(p, s); }
   else { if (p.is_bf16) dispatch_fwd<128, true>(p, s); else dispatch_fwd<128, false>(p, s); }

@@ -40,7 +40,9 @@ struct Fwd2Tma {
   CUtensorMap q, k, v;
 };
 
-template <int HD, int QT> struct F2 {
+// EB = bytes per q/k/v element: 2 (bf16 / fp16) or 1 (e4m3, the FP8 forward of csrc/flashmask_v2/flash_api.cu:107-131;
+// out stays 16-bit).  Shared-memory tiles are 128 rows of HD * EB bytes in 128-byte swizzled boxes either way.
+template <int HD, int QT, int EB = 2> struct F2 {
   static constexpr int kQT = QT;                                         // Q tiles per CTA (2 needs 256 + 2 HD <= 512 TMEM columns)
   static constexpr int kStages = HD <= 128 ? (QT == 2 ? 4 : 5) : (HD <= 192 ? 3 : 2);    // K/V ring depth (tiles of 128 x HD)
   static constexpr int kSmWarps = 8 * kQT;                               // softmax warps: two warpgroups per Q tile
@@ -50,10 +52,13 @@ template <int HD, int QT> struct F2 {
   static constexpr int kSmRegs = QT == 2 ? 104 : 200;                    // register budget of a softmax thread
   static constexpr int kAuxRegs = QT == 2 ? 64 : 96;                     // ... of an issuer / producer / idle thread
   static_assert(kSmWarps * 32 * kSmRegs + 128 * kAuxRegs <= kThreads * (QT == 2 ? 96 : 168), "register pool of the CTA");
-  static constexpr int kTileBytes = kBM * HD * 2;
+  static constexpr int kTileBytes = kBM * HD * EB;
+  static constexpr int kOTileBytes = kBM * HD * 2;                       // one staged output tile (16-bit)
   static constexpr int kQOff = 0;
   static constexpr int kKVOff = kQT * kTileBytes;
-  static constexpr int kXchOff = kKVOff + kStages * kTileBytes;          // row-max exchange: [2 parities][kQT][2 halves][128]
+  // output staging: 16-bit inputs reuse the (dead) Q tile; an e4m3 Q tile is half the size of its output tile
+  static constexpr int kOStageOff = EB == 2 ? kQOff : kKVOff + kStages * kTileBytes;
+  static constexpr int kXchOff = kKVOff + kStages * kTileBytes + (EB == 2 ? 0 : kQT * kOTileBytes);  // row-max exchange: [2 parities][kQT][2 halves][128]
   static constexpr int kSumOff = kXchOff + 2 * kQT * 2 * kBM * 4;        // row-sum exchange: [kQT][2 halves][128]
   static constexpr int kBarOff = kSumOff + kQT * 2 * kBM * 4;
   static constexpr int kNumBars = 4 + 2 * kStages + 8;
@@ -159,11 +164,12 @@ __device__ __forceinline__ float exp2_poly(float x) {
   return __int_as_float(__float_as_int(q) + (__float_as_int(jm) << 23));
 }
 
-template <int HD, bool kBf16, int QT>
-__global__ void __launch_bounds__(F2<HD, QT>::kThreads, 1)
+template <int HD, bool kBf16, int QT, int EB>
+__global__ void __launch_bounds__(F2<HD, QT, EB>::kThreads, 1)
 fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm_param, const Fwd2Tma *__restrict__ tm_dev,
             int num_m, int num_tiles) {
-  using L = F2<HD, QT>;
+  using L = F2<HD, QT, EB>;
+  constexpr bool kFp8 = EB == 1;
   const Fwd2Tma &tm = tm_dev ? *tm_dev : tm_param;   // device-patched maps (flat varlen symbols) or the launch's own
   constexpr int kQT = L::kQT, kStages = L::kStages, kSmWarps = L::kSmWarps;
   extern __shared__ uint8_t smem_raw[];
@@ -206,7 +212,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
   tc_fence_after();
   const uint32_t tmem_raw = *tmem_slot;
 
-  constexpr int kBoxes = HD / 64;              // 64-element (128-byte) boxes per row
+  constexpr int kBoxes = HD * EB / 128;        // 128-byte boxes per row
+  constexpr int kBoxElems = 128 / EB;          // elements per box row
   constexpr uint32_t kBoxBytes = kBM * 128;    // one box: 128 rows x 128 bytes
 
   if (warp >= kSmWarps) {
@@ -223,7 +230,7 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
           mbar_expect_tx(bar(B_KVFULL + st), L::kTileBytes);
 #pragma unroll
           for (int bx = 0; bx < kBoxes; ++bx)
-            tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + bx * kBoxBytes, m, bar(B_KVFULL + st), bx * 64, ti.hk,
+            tma_load_4d(sbase + L::kKVOff + st * L::kTileBytes + bx * kBoxBytes, m, bar(B_KVFULL + st), bx * kBoxElems, ti.hk,
                         ti.k_row0 + j * kBN, ti.k_b);
           ++kv_it;
         };
@@ -232,7 +239,7 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
           mbar_expect_tx(bar(B_QFULL + t), L::kTileBytes);
 #pragma unroll
           for (int bx = 0; bx < kBoxes; ++bx)
-            tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + bx * kBoxBytes, &tm.q, bar(B_QFULL + t), bx * 64, ti.hq,
+            tma_load_4d(sbase + L::kQOff + t * L::kTileBytes + bx * kBoxBytes, &tm.q, bar(B_QFULL + t), bx * kBoxElems, ti.hq,
                         ti.q_row0 + ti.m0 + t * kBM, ti.q_b);
           ++qcnt[t];
         };
@@ -267,8 +274,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
       // ======================= MMA issuer =======================
       // The whole warp runs the control flow (descriptors stay in uniform registers); one elected lane issues.
       const uint32_t tmem = bc0((int)tmem_raw);
-      constexpr uint32_t idesc_s = make_idesc(kBf16, kBM, kBN, false, false);
-      constexpr uint32_t idesc_o = make_idesc(kBf16, kBM, HD, false, true);
+      constexpr uint32_t idesc_s = kFp8 ? make_idesc_e4m3(kBM, kBN, false) : make_idesc(kBf16, kBM, kBN, false, false);
+      constexpr uint32_t idesc_o = kFp8 ? make_idesc_e4m3(kBM, HD, true) : make_idesc(kBf16, kBM, HD, false, true);
       uint32_t kv_it = 0, qcnt[2] = {0, 0}, pcnt[2] = {0, 0};
       auto commit = [&](uint32_t b) {
         if (elect_one()) umma_commit(b);
@@ -286,10 +293,14 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
         const uint32_t ka = sbase + L::kKVOff + kstage * L::kTileBytes;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < HD / 16; ++k) {
+          for (int k = 0; k < HD * EB / 32; ++k) {       // 32 bytes of the head dim per instruction (K16 x 16-bit, K32 x 8-bit)
             const uint32_t off = (k / 4) * kBoxBytes + (k % 4) * 32;
-            umma_ss(tmem + slot * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
-                    k > 0);
+            if constexpr (kFp8)
+              umma_ss_f8(tmem + slot * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
+                         k > 0);
+            else
+              umma_ss(tmem + slot * kBN, make_sdesc_sw128(qa + off, 16, 1024), make_sdesc_sw128(ka + off, 16, 1024), idesc_s,
+                      k > 0);
           }
           umma_commit(bar(B_SFULL + slot));
         }
@@ -300,10 +311,15 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
         const uint32_t va = sbase + L::kKVOff + vstage * L::kTileBytes;
         if (elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < kBN / 32; ++kk) {
-            const int k = half * (kBN / 32) + kk;
-            umma_ts(tmem + 2 * kBN + t * HD, tmem + slot * kBN + k * 8, make_sdesc_sw128(va + k * 2048, kBoxBytes, 1024),
-                    idesc_o, (accumulate || k > 0) ? 1u : 0u);
+          constexpr int kKeys = 32 / EB;                  // keys per instruction: P is packed 2 (16-bit) or 4 (e4m3) per column
+          for (int kk = 0; kk < kBN / 2 / kKeys; ++kk) {
+            const int k = half * (kBN / 2 / kKeys) + kk;
+            if constexpr (kFp8)
+              umma_ts_f8(tmem + 2 * kBN + t * HD, tmem + slot * kBN + k * 8, make_sdesc_sw128(va + k * (kKeys * 128), kBoxBytes, 1024),
+                         idesc_o, (accumulate || k > 0) ? 1u : 0u);
+            else
+              umma_ts(tmem + 2 * kBN + t * HD, tmem + slot * kBN + k * 8, make_sdesc_sw128(va + k * (kKeys * 128), kBoxBytes, 1024),
+                      idesc_o, (accumulate || k > 0) ? 1u : 0u);
           }
           // completion of this P V.  One Q tile: signalled per S SLOT, because there S runs two key blocks ahead of P V and
           // a single barrier could be two phases ahead of a waiter (a parity wait cannot tell phase n from phase n + 2)
@@ -429,8 +445,9 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
     const uint32_t tmem = tmem_raw;
     constexpr int kHalfCols = HD / 2;           // O columns per thread
     const uint32_t tO = tmem + lane_base + 2 * kBN + t * HD + hf * kHalfCols;
-    const float scale_nat = p.softmax_scale;
-    const float scale_log2 = scale_nat * kLog2e;
+    float scale_nat = p.softmax_scale;
+    float scale_log2 = scale_nat * kLog2e;
+    float out_scale = 1.f;
     float *xch = (float *)(smem + L::kXchOff);  // [parity][t][hf][row]
     float *xsum = (float *)(smem + L::kSumOff); // [t][hf][row]
     uint32_t g = 0;       // key blocks processed by this thread so far (all tiles)
@@ -446,6 +463,15 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
       const MaskCtx mc = make_mask_ctx(p, ti.bi, ti.hq, ti.sq, ti.sk);
       const int shiftc = mc.bottom_right ? mc.shift : 0;
       const int r0 = ti.m0 + t * kBM;
+      if constexpr (kFp8) {
+        // per (batch, kv head) dequantisation factors: logits by q_descale * k_descale, out by v_descale
+        // (csrc/flashmask_v2/mainloop_fwd_sm90_tma_gmma_ws.hpp:1612-1614,1868-1869)
+        const float qd = p.q_descale ? p.q_descale[ti.bi * p.q_descale_batch_stride + ti.hk * p.q_descale_head_stride] : 1.f;
+        const float kd = p.k_descale ? p.k_descale[ti.bi * p.k_descale_batch_stride + ti.hk * p.k_descale_head_stride] : 1.f;
+        out_scale = p.v_descale ? p.v_descale[ti.bi * p.v_descale_batch_stride + ti.hk * p.v_descale_head_stride] : 1.f;
+        scale_nat = p.softmax_scale * qd * kd;
+        scale_log2 = scale_nat * kLog2e;
+      }
       float m_ref = -CUDART_INF_F, l = 0.f;
       const int nb_total = ti.n_hi[t] - ti.n_lo[t];
       for (int nb = 0; nb < nb_total; ++nb, ++g) {
@@ -453,7 +479,7 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
         const uint32_t slot = kQT == 2 ? (uint32_t)t : (g & 1u);
         const uint32_t par = kQT == 2 ? (g & 1u) : ((g >> 1) & 1u);
         const uint32_t tS = tmem + lane_base + slot * kBN + hf * 64;
-        const uint32_t tP = tmem + lane_base + slot * kBN + hf * 32;
+        const uint32_t tP = tmem + lane_base + slot * kBN + hf * (kFp8 ? 16 : 32);   // this thread's 64 weights: 32 / 16 columns
         mbar_wait(bar(B_SFULL + slot), par);
         tc_fence_after();
         uint32_t s[2][32];
@@ -520,9 +546,11 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
         const float msc = (m_ref == -CUDART_INF_F) ? 0.f : m_ref * scale_log2;
         const uint64_t sc2 = pk2(scale_log2, scale_log2), nm2 = pk2(-msc, -msc);
         uint64_t suma = pk2(0.f, 0.f), sumb = pk2(0.f, 0.f);
+        uint32_t pk8[16];      // e4m3: the 64 weights of this thread, four per column
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t pk[16];
+          float pprev0 = 0.f, pprev1 = 0.f;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const uint64_t x2 = ffma2(pk2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, nm2);
@@ -535,10 +563,16 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
               p0 = ex2(x0); p1 = ex2(x1);
             }
             if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
-            pk[i] = pack2<kBf16>(p0, p1);
+            if constexpr (kFp8) {
+              if (i & 1) pk8[c * 8 + i / 2] = pack4_e4m3(pprev0, pprev1, p0, p1);
+              else { pprev0 = p0; pprev1 = p1; }
+            } else {
+              pk[i] = pack2<kBf16>(p0, p1);
+            }
           }
-          tmem_st16(tP + c * 16, pk);
+          if constexpr (!kFp8) tmem_st16(tP + c * 16, pk);
         }
+        if constexpr (kFp8) tmem_st16(tP, pk8);
         {
           float a0, a1;
           unpk2(fadd2(suma, sumb), a0, a1);
@@ -572,8 +606,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
       // A row with at least one visible key has l >= ~1 (its maximum contributes 2^0).  Masked elements that went
       // through the polynomial exp2 contribute 2^-125 each instead of 0, so "no visible key" is l below a tiny bound.
       const bool nonempty = l > 1e-30f;
-      const float inv = nonempty ? 1.f / l : 0.f;
-      uint8_t *stage = smem + L::kQOff + t * L::kTileBytes;  // Q_t is dead: all S MMAs of this tile have completed
+      const float inv = nonempty ? out_scale / l : 0.f;
+      uint8_t *stage = smem + L::kOStageOff + t * L::kOTileBytes;  // 16-bit inputs: Q_t, dead once this tile's S MMAs have completed
       constexpr int kChunks = HD / 8;                        // 16-byte chunks per row
 #pragma unroll
       for (int c = 0; c < kHalfCols / 32; ++c) {
@@ -618,22 +652,23 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
 void sanitize2(TmaDesc4 &d) {
   // a dimension of extent 1 never advances: give it a legal, monotonic stride
   for (int i = 1; i < 4; ++i)
-    if (d.dims[i] == 1) d.strides[i - 1] = (i == 1 ? d.dims[0] * 2 : d.strides[i - 2] * d.dims[i - 1] + 15) / 16 * 16;
+    if (d.dims[i] == 1) d.strides[i - 1] = (i == 1 ? d.dims[0] * d.elem_bytes : d.strides[i - 2] * d.dims[i - 1] + 15) / 16 * 16;
 }
 
-TmaDesc4 desc2(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch, int box_rows) {
+TmaDesc4 desc2(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batch, int box_rows, int eb = 2) {
   TmaDesc4 x;
   x.ptr = t.ptr;
+  x.elem_bytes = eb;
   x.dims[0] = (uint64_t)d; x.dims[1] = (uint64_t)heads; x.dims[2] = (uint64_t)rows; x.dims[3] = (uint64_t)batch;
-  x.strides[0] = (uint64_t)t.head_stride * 2; x.strides[1] = (uint64_t)t.row_stride * 2;
-  x.strides[2] = (uint64_t)t.batch_stride * 2;
-  x.box[0] = 64; x.box[1] = 1; x.box[2] = (uint32_t)box_rows; x.box[3] = 1;
+  x.strides[0] = (uint64_t)t.head_stride * eb; x.strides[1] = (uint64_t)t.row_stride * eb;
+  x.strides[2] = (uint64_t)t.batch_stride * eb;
+  x.box[0] = 128 / eb; x.box[1] = 1; x.box[2] = (uint32_t)box_rows; x.box[3] = 1;
   sanitize2(x);
   return x;
 }
 
-template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1)> void launch_fwd2(const Params &p, cudaStream_t s) {
-  using L = F2<HD, QT>;
+template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2> void launch_fwd2(const Params &p, cudaStream_t s) {
+  using L = F2<HD, QT, EB>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
   // packed tensors without host-known totals (the flat varlen symbols): the row extents are patched on the device
@@ -642,9 +677,9 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1)> void launch_fwd2(con
   const int64_t rows_k = packed_k ? (p.total_k >= 0 ? p.total_k : (int64_t)p.b * p.seqlen_k) : p.seqlen_k;
   Fwd2Tma tm;
   // columns at or beyond p.d (head dims that are not a multiple of 64) are zero-filled by the TMA unit
-  tm.q = make_tma_4d(desc2(p.q, p.d, p.h, rows_q, packed_q ? 1 : p.b, kBM));
-  tm.k = make_tma_4d(desc2(p.k, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
-  tm.v = make_tma_4d(desc2(p.v, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN));
+  tm.q = make_tma_4d(desc2(p.q, p.d, p.h, rows_q, packed_q ? 1 : p.b, kBM, EB));
+  tm.k = make_tma_4d(desc2(p.k, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN, EB));
+  tm.v = make_tma_4d(desc2(p.v, p.d, p.h_k, rows_k, packed_k ? 1 : p.b, kBN, EB));
   Fwd2Tma *tm_dev = nullptr;
   if (dev_rows) {
     const int k_like[3] = {0, 1, 1};
@@ -652,7 +687,7 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1)> void launch_fwd2(con
   }
   const int num_m = ceil_div(p.seqlen_q, kBM * L::kQT);
   const int num_tiles = p.b * p.h * num_m;
-  auto kern = fwd2_kernel<HD, kBf16, QT>;
+  auto kern = fwd2_kernel<HD, kBf16, QT, EB>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
@@ -671,6 +706,13 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1)> void launch_fwd2(con
 // kernel of sm100_fwd.cu, head dims <= 128 only).
 bool sm100_fwd2_eligible(const Params &p) {
   return p.lt_start == nullptr && p.p_dropout == 0.f && p.attn_mask == nullptr && p.softcap == 0.f;
+}
+
+// FP8 (e4m3) forward: same kernel with byte operands, tcgen05.mma kind::f8f6f4 (twice the 16-bit rate), P rounded to
+// e4m3 for the P V product as the reference's sm90 FP8 path does, output in bf16.
+void sm100_fwd2_e4m3(const Params &p, cudaStream_t s) {
+  if (p.d <= 128) launch_fwd2<128, true, 2, 1>(p, s);
+  else launch_fwd2<256, true, 1, 1>(p, s);
 }
 
 void sm100_fwd2(const Params &p, cudaStream_t s) {

@@ -35,7 +35,7 @@ CUtensorMap make_tma_4d(const TmaDesc4 &d) {
   cuuint64_t strides[3] = {d.strides[0], d.strides[1], d.strides[2]};
   cuuint32_t box[4] = {d.box[0], d.box[1], d.box[2], d.box[3]};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(d.ptr), dims, strides, box, estr,
+  CUresult r = encode_fn()(&m, d.elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(d.ptr), dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)

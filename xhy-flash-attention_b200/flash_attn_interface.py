@@ -630,3 +630,64 @@ def flash_attn_with_kvcache(q, k_cache, v_cache, k=None, v=None, rotary_cos=None
         else:
             _capi.check(lib.fa_b200_fwd_splitkv(p, stream), "fa_b200_fwd_splitkv")
     return (out, lse) if return_softmax_lse else out
+
+
+def flash_attn_fp8_func(q, k, v, q_descale=None, k_descale=None, v_descale=None, softmax_scale=None, causal=False, *,
+                        window_size=(-1, -1), cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=None, max_seqlen_k=None):
+    """FP8 forward: ``q, k, v`` are ``torch.float8_e4m3fn`` tensors, ``*_descale`` optional fp32 ``(batch, heads_k)``
+    dequantisation factors; returns ``(out, softmax_lse)`` with ``out`` in bf16.  Forward only.
+
+    The fork has this capability at C level only (``is_e4m3`` + ``*_descale_ptr`` of the FlashMask-v2 / FA3 handle,
+    csrc/flashmask_v2/flash.h:55-63,144; dispatch csrc/flashmask_v2/flash_api.cu:107-131): logits are
+    ``softmax_scale * q_descale * k_descale * (q8 . k8)``, the weights are rounded to e4m3 for the P V product, the
+    result is multiplied by ``v_descale`` (mainloop_fwd_sm90_tma_gmma_ws.hpp:1612-1614,1868-1869).  Causal masks are
+    bottom-right aligned as everywhere on that surface.  Fixed-length ``(b, s, h, d)`` or packed ``(total, h, d)`` with
+    ``cu_seqlens_*``; head dim a multiple of 16 up to 256.
+    """
+    if q.dtype != torch.float8_e4m3fn or k.dtype != q.dtype or v.dtype != q.dtype:
+        raise RuntimeError("flash_attn_fp8_func takes float8_e4m3fn q, k, v")
+    q, k, v = [_maybe_contiguous(x) for x in (q, k, v)]
+    varlen = cu_seqlens_q is not None
+    d = q.shape[-1]
+    if d % 16 != 0 or d > 256:
+        raise RuntimeError("FP8 forward needs a head dimension that is a multiple of 16, at most 256")
+    p = new_params(torch.bfloat16)
+    p.is_e4m3 = 1
+    if varlen:
+        total_q, h, _ = q.shape
+        h_k = k.shape[1]
+        b = cu_seqlens_q.numel() - 1
+        sq, sk = int(max_seqlen_q), int(max_seqlen_k)
+        p.cu_seqlens_q, p.cu_seqlens_k = cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr()
+        p.total_q, p.total_k = total_q, k.shape[0]
+        out = torch.empty((total_q, h, d), dtype=torch.bfloat16, device=q.device)
+    else:
+        b, sq, h, _ = q.shape
+        sk, h_k = k.shape[1], k.shape[2]
+        out = torch.empty((b, sq, h, d), dtype=torch.bfloat16, device=q.device)
+    if h % h_k != 0:
+        raise RuntimeError("Number of heads in key/value must divide number of heads in query")
+    lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
+    p.q, p.k, p.v, p.o = [tdesc(t, packed=varlen) for t in (q, k, v, out)]
+    p.softmax_lse = lse.data_ptr()
+    p.b, p.seqlen_q, p.seqlen_k, p.h, p.h_k, p.d = b, sq, sk, h, h_k, d
+    p.seqlen_q_rounded, p.seqlen_k_rounded, p.d_rounded = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+    p.softmax_scale = d ** -0.5 if softmax_scale is None else softmax_scale
+    p.is_causal = 1 if causal else 0
+    p.causal_bottom_right = 1
+    p.lse_empty_is_neg_inf = 1
+    p.window_left, p.window_right = int(window_size[0]), int(window_size[1])
+    keep = []
+    for name, t in (("q", q_descale), ("k", k_descale), ("v", v_descale)):
+        if t is None:
+            continue
+        if t.dtype != torch.float32 or tuple(t.shape) != (b, h_k):
+            raise RuntimeError(f"{name}_descale must be fp32 of shape (batch, heads_k)")
+        keep.append(t)
+        setattr(p, f"{name}_descale", t.data_ptr())
+        setattr(p, f"{name}_descale_batch_stride", t.stride(0))
+        setattr(p, f"{name}_descale_head_stride", t.stride(1))
+    with torch.cuda.device(q.device):
+        _capi.check(_capi.load().fa_b200_fwd(p, _capi.stream_ptr(q.device)), "fa_b200_fwd")
+    del keep
+    return out, lse
