@@ -153,6 +153,19 @@ bool fa_b200_fwd_splitkv(const fa_b200_params *p, cudaStream_t stream);
  * (csrc/flash_attn_v3/flash_fwd_combine_kernel.h:194-478). */
 bool fa_b200_fwd_combine(const fa_b200_params *p, cudaStream_t stream);
 
+/* Split-KV decode + combine in ONE call that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  Same params as fa_b200_fwd_splitkv, with oaccum and lseaccum NULL: the split partials live
+ * in a static __device__ array of FA_B200_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it until
+ * the process exits); writes o and softmax_lse.  A call needs num_splits * b * seqlen_q * h * (d + 1) * 4 bytes of it and
+ * is rejected (false + flash_attn_error()) when that exceeds the array.  cu_seqlens_*, FlashMask, num_splits_dynamic and
+ * is_e4m3 are rejected; seqused_k, paged / indexed / left-padded caches, causal / window masks are taken as usual.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device share the array: calls that overlap on the
+ * GPU (different streams or threads) race -- keep them on one stream.  Nothing in the array needs clearing between
+ * calls (every partial a call reads it has written first). */
+#define FA_B200_NOALLOC_SCRATCH_BYTES (16u << 20)
+bool fa_b200_fwd_splitkv_noalloc(const fa_b200_params *p, cudaStream_t stream);
+
 /* Split heuristic.  Equivalent of fa3_get_num_splits (csrc/flashmask_v2/heuristics.h:22-59). */
 int fa_b200_num_splits(int batch, int num_heads_k, int seqlen_q_packed, int seqlen_k, int head_size, int num_sm);
 

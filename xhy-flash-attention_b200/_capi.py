@@ -77,7 +77,7 @@ def load() -> C.CDLL:
             "(there is no CPU or PyTorch fallback for the attention kernels)")
     lib = C.CDLL(LIB_PATH)
     pp = C.POINTER(Params)
-    for name in ("fa_b200_fwd", "fa_b200_bwd", "fa_b200_fwd_splitkv", "fa_b200_fwd_combine"):
+    for name in ("fa_b200_fwd", "fa_b200_bwd", "fa_b200_fwd_splitkv", "fa_b200_fwd_combine", "fa_b200_fwd_splitkv_noalloc"):
         fn = getattr(lib, name)
         fn.argtypes = [pp, C.c_void_p]
         fn.restype = C.c_bool

@@ -43,6 +43,7 @@ int device_cc_major();
 void run_fwd(const Params &p, cudaStream_t s);
 void run_bwd(const Params &p, cudaStream_t s);
 void run_splitkv(const Params &p, cudaStream_t s);
+void run_splitkv_noalloc(const Params &p, cudaStream_t s);   // noalloc.cu: partials in a static __device__ array
 
 // ---- kernel families -------------------------------------------------------------------------
 // generic SIMT kernels: any head_size % 8 == 0 up to 256, every mask kind, both dtypes.
