@@ -413,6 +413,9 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
         FB_TR(2, it, 2);
         tc_fence_after();
         tmem_a_mn_b(TDV, TS_, sDO, it > 0, bar(BB_DO_EMPTY));
+        // S(it+1) goes here, BEFORE dK(it) / dQ(it): its P phase (the longest compute phase) then runs under those two MMAs.
+        // Measured alternative (round 2): S(it+1) behind dQ(it), to fill the bubble while the reducers drain dQ(it) out of
+        // the dP/dS/dQ region -- 16 % slower on C3 (9.73 -> 11.32 ms), 26 % at d64: P(it+1) arrives too late for dV(it+1).
         if (it + 1 < n_it_u) {
           mbar_wait(bar(BB_Q_FULL + (st ^ 1)), ((it + 1) >> 1) & 1);
           tc_fence_after();

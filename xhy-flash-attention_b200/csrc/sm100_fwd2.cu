@@ -310,8 +310,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
       auto issue_pv_half = [&](int t, int slot, uint32_t vstage, int half, bool accumulate) {
         const uint32_t va = sbase + L::kKVOff + vstage * L::kTileBytes;
         if (elect_one()) {
-#pragma unroll
           constexpr int kKeys = 32 / EB;                  // keys per instruction: P is packed 2 (16-bit) or 4 (e4m3) per column
+#pragma unroll
           for (int kk = 0; kk < kBN / 2 / kKeys; ++kk) {
             const int k = half * (kBN / 2 / kKeys) + kk;
             if constexpr (kFp8)
