@@ -112,6 +112,9 @@ _CUDA_OPS = RingOps()
 # ----------------------------------------------------------------------------------------------------
 # communication: one rotation of a list of tensors to rank+1, received from rank-1
 # ----------------------------------------------------------------------------------------------------
+STALL_TRACE = None     # set to a list to collect (tag, event before, event after) around every wait for a transfer
+
+
 class _Rotation:
     """Posts send(to next) / recv(from prev) for a list of tensors; ``wait()`` returns the received tensors.
 
@@ -119,7 +122,8 @@ class _Rotation:
     caller's stream; ``wait()`` makes the caller's stream wait for the transfer.
     """
 
-    def __init__(self, group, tensors, comm_stream=None, exchange=True):
+    def __init__(self, group, tensors, comm_stream=None, exchange=True, tag=""):
+        self.tag = tag
         if not exchange:                      # compute-only replay (RingOps.exchange)
             self.recv, self.reqs, self.staged, self.stream, self.keep = list(tensors), [], None, None, []
             return
@@ -156,7 +160,15 @@ class _Rotation:
                 dst.copy_(src)
             return self.staged
         if self.stream is not None:
-            torch.cuda.current_stream().wait_stream(self.stream)
+            cur = torch.cuda.current_stream()
+            if STALL_TRACE is not None:          # diagnostics: how long the compute stream sits in this wait
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(cur)
+                cur.wait_stream(self.stream)
+                e1.record(cur)
+                STALL_TRACE.append((self.tag, e0, e1))
+            else:
+                cur.wait_stream(self.stream)
             for t in self.keep + self.recv:      # allocated on the compute stream, used by the comm stream
                 t.record_stream(self.stream)
         return self.recv
@@ -198,7 +210,7 @@ def ring_forward(q, k, v, softmax_scale, causal, group=None, ops: RingOps = _CUD
     comm = _comm_stream(q)
     k_cur, v_cur = k.contiguous(), v.contiguous()
     for t in range(world):
-        rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange) if t + 1 < world else None
+        rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange, f"fwd kv {t}") if t + 1 < world else None
         src = (rank - t) % world
         plan = _step_plan(causal, rank, src)
         if plan is not None:
@@ -224,7 +236,7 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, causal, group=None, op
     acc_rot = None
     half = q.shape[1] // 2
     for t in range(world):
-        kv_rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange) if t + 1 < world else None
+        kv_rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange, f"fwd kv {t}") if t + 1 < world else None
         src = (rank - t) % world
         plan = _step_plan(causal, rank, src)
         dk_blk = dv_blk = None
@@ -240,7 +252,7 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, causal, group=None, op
         if dk_blk is not None:
             _part(dk_acc, dk_blk[0]).add_(dk_blk[1])
             _part(dv_acc, dv_blk[0]).add_(dv_blk[1])
-        acc_rot = _Rotation(group, [dk_acc, dv_acc], comm, ops.exchange)   # travels with the block; after `world` hops it is home
+        acc_rot = _Rotation(group, [dk_acc, dv_acc], comm, ops.exchange, f"bwd acc {t}")   # travels with the block; after `world` hops it is home
         if kv_rot is not None:
             k_cur, v_cur = kv_rot.wait()
     dk_acc, dv_acc = acc_rot.wait()
