@@ -143,6 +143,72 @@ template <int mode> __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(
   }
 }
 
+// Mixed use: TMEM allocated with cta_group::2; the leader alternates pair MMAs (M 256, N 128, into columns [0,128)) with
+// its own cta_group::1 MMAs (M 128, N 64, into columns [128,192)) while the peer CTA issues cta_group::1 MMAs of its own.
+// Is that legal on the hardware (results checked) and what does it cost?
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(160, 1) mix(int iters, long long *out, int *bad) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const uint32_t rank = cluster_ctarank();
+  __shared__ uint32_t tmem_slot;
+  __shared__ __align__(8) unsigned long long mbar[4], mbar1[4];
+  uint8_t *A = smem, *B = smem + 32768;          // A: 128 x 128; B: 64 x 128 (this CTA's half of the pair's N = 128)
+  for (int i = threadIdx.x; i < 128 * 128; i += blockDim.x) put(A, 128, i / 128, i % 128, (float)((i / 128 + 128 * rank) % 7 + 1));
+  for (int i = threadIdx.x; i < 64 * 128; i += blockDim.x) put(B, 64, i / 128, i % 128, (float)((i / 128 + 64 * rank) % 5 + 1));
+  if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&mbar[i]), 1); mbar_init(smem_u32(&mbar1[i]), 1); } fence_mbar_init(); }
+  fence_proxy_async_smem();
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before(); __syncthreads(); cluster_sync_all(); tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (warp == 4) {
+    constexpr uint32_t idesc2 = make_idesc(true, 256, 128, false, false), idesc1 = make_idesc(true, 128, 64, false, false);
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      if (it >= 4) { if (rank == 0) mbar_wait(smem_u32(&mbar[it % 4]), ((it - 4) / 4) & 1); mbar_wait(smem_u32(&mbar1[it % 4]), ((it - 4) / 4) & 1); }
+      if (elect_one()) {
+        if (rank == 0) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ss_pair(tmem, make_sdesc_sw128(sbase + (k / 4) * 16384 + (k % 4) * 32, 16, 1024),
+                         make_sdesc_sw128(sbase + 32768 + (k / 4) * 8192 + (k % 4) * 32, 16, 1024), idesc2, k > 0);
+          umma_commit_pair(smem_u32(&mbar[it % 4]), 1);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_ss(tmem + 128, make_sdesc_sw128(sbase + (k / 4) * 16384 + (k % 4) * 32, 16, 1024),
+                  make_sdesc_sw128(sbase + 32768 + (k / 4) * 8192 + (k % 4) * 32, 16, 1024), idesc1, k > 0);
+        umma_commit(smem_u32(&mbar1[it % 4]));
+      }
+      __syncwarp();
+    }
+    for (int it = iters - 4; it < iters; ++it) { if (rank == 0) mbar_wait(smem_u32(&mbar[it % 4]), (it / 4) & 1); mbar_wait(smem_u32(&mbar1[it % 4]), (it / 4) & 1); }
+    if (lane == 0 && blockIdx.x < 2) out[8 + rank] = clock64() - t0;
+  }
+  tc_fence_before(); __syncthreads(); cluster_sync_all(); tc_fence_after();
+  if (warp < 4) {
+    uint32_t v[32];
+    const uint32_t base = tmem + ((uint32_t)(warp * 32) << 16);
+    int nbad = 0;
+    const int m = warp * 32 + lane + 128 * rank;
+    for (int c = 0; c < 6; ++c) {                 // columns [0,128): pair product; [128,192): this CTA's own product
+      tmem_ld32(base + c * 32, v);
+      tmem_wait_ld();
+      for (int i = 0; i < 32; ++i) {
+        const int n = c < 4 ? c * 32 + i : (c - 4) * 32 + i + 64 * rank;
+        if (__uint_as_float(v[i]) != 128.f * (m % 7 + 1) * (n % 5 + 1)) ++nbad;
+      }
+    }
+    if (nbad) atomicAdd(bad + 8, nbad);
+  }
+  tc_fence_before(); __syncthreads(); cluster_sync_all();
+  if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+
 int main() {
   long long *out;
   int *bad;
@@ -171,5 +237,15 @@ int main() {
     cudaMemcpy(hb, bad, sizeof(hb), cudaMemcpyDeviceToHost);
     printf("%-16s %-45s %.0f cycles per 128x128x128 per SM   wrong elements: %d\n", pat[pattern], names[mode], (double)h[mode] / iters, hb[mode]);
   }
+  cudaFuncSetAttribute(mix, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536 + 2048);
+  for (int rep = 0; rep < 2; ++rep) mix<<<148, 160, 65536 + 1024>>>(iters, out, bad);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { printf("mixed cta_group error: %s\n", cudaGetErrorString(e)); return 1; }
+  long long h[16];
+  int hb[16];
+  cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaMemcpy(hb, bad, sizeof(hb), cudaMemcpyDeviceToHost);
+  printf("mixed: pair SS 128^3 + own cta_group::1 SS (M128 N64 K128) per iteration: leader %.0f cycles, peer (cta_group::1 only) %.0f cycles; wrong elements: %d\n",
+         (double)h[8] / iters, (double)h[9] / iters, hb[8]);
   return 0;
 }

@@ -449,7 +449,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
     // ======================= dQ reducers =======================
     // All of dQ (128 fp32 per row) is pulled out of TMEM first so that the dP/dS/dQ region is handed back to the MMA
     // warp as early as possible; the smem staging + bulk reduce-add then runs off the critical path.
-    setmaxnreg_inc<184>();
+    setmaxnreg_inc<kDrop ? 168 : 184>();   // the dropout instantiation moves 16 registers per thread to the compute warpgroups
     const int r = (warp % 4) * 32 + lane;
     const uint32_t lane_base = (uint32_t)((warp % 4) * 32) << 16;
     const int tid = threadIdx.x - 256;
@@ -510,7 +510,7 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
     if (tid == 0) bulk_wait<0>();
   } else {
     // ======================= compute warpgroups =======================
-    setmaxnreg_inc<136>();
+    setmaxnreg_inc<kDrop ? 144 : 136>();
     const int wg = warp / 4;
     const int r = (warp % 4) * 32 + lane;          // key row inside the block == TMEM lane
     const int col = t.n0 + r;                      // key index
@@ -567,29 +567,34 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
       }
       // Dropout (kDrop): keep bits of this thread's 64 (query, key) pairs.  The mask is dropout_keep() of common.h: one
       // Philox call covers 16 consecutive KEY columns of one query row, i.e. the 16 lanes of a half warp want one byte
-      // each of the same call.  Each lane therefore runs the generator for one row of a 16-row group and the half
-      // warp exchanges the results by shuffles (16 steps: at step s a lane serves the lane s places below it and is
-      // served by the lane s places above).  Done before the wait for S, under the MMA that is in flight.
+      // each of the same call.  Each lane therefore runs the generator for one row of a 16-row group, turns its 16 bytes
+      // into a 16-bit keep mask (bit j = column j of its row), and the half warp TRANSPOSES the 16 x 16 bit matrix with
+      // four butterfly exchanges (rows on lanes -> columns on lanes): lane j ends up with the 16 rows of its own column.
+      // (Round 1 exchanged the bytes themselves in 16 shuffle steps: 2.4 x the instructions.)  Done before the wait for S,
+      // under the MMA that is in flight.
       uint32_t kb[2] = {0xffffffffu, 0xffffffffu};
       if constexpr (kDrop) {
         kb[0] = kb[1] = 0u;
         const int l16 = lane & 15;
-        const uint32_t thr = (uint32_t)floorf((1.f - p.p_dropout) * 255.f);
+        const uint32_t thr4 = (uint32_t)floorf((1.f - p.p_dropout) * 255.f) * 0x01010101u;
         const uint64_t ncg = (uint64_t)((p.seqlen_k + 15) / 16);
         const uint64_t cg = (uint64_t)((t.n0 + (warp % 4) * 32 + (lane & 16)) >> 4);
         const uint64_t head_base = ((uint64_t)t.bi * p.h + hq) * (uint64_t)p.seqlen_q;
+        auto keep4 = [&](uint32_t w) {   // 4 bytes -> 4 bits: bit b = (byte b <= threshold)
+          return ((__vcmpleu4(w, thr4) & 0x08040201u) * 0x01010101u) >> 24;
+        };
 #pragma unroll
         for (int ig = 0; ig < 4; ++ig) {
           const uint64_t rrow = (uint64_t)(m0 + wg * 64 + ig * 16 + l16);
-          const uint4 rnd = philox4x32_10(p.philox_seed, (head_base + rrow) * ncg + cg, p.philox_offset);
+          const uint4 rnd = philox4x32_7(p.philox_seed, (head_base + rrow) * ncg + cg, p.philox_offset);
+          uint32_t x = keep4(rnd.x) | (keep4(rnd.y) << 4) | (keep4(rnd.z) << 8) | (keep4(rnd.w) << 12);
 #pragma unroll
-          for (int s_ = 0; s_ < 16; ++s_) {
-            const int wi = ((l16 - s_) & 15) >> 2;         // word the lane I serve at this step wants
-            const uint32_t wsel = wi == 0 ? rnd.x : wi == 1 ? rnd.y : wi == 2 ? rnd.z : rnd.w;
-            const int src16 = (l16 + s_) & 15;             // row (inside the group) I am served with
-            const uint32_t got = __shfl_sync(0xffffffffu, wsel, (lane & 16) | src16);
-            if (((got >> ((l16 & 3) * 8)) & 0xffu) <= thr) kb[ig >> 1] |= 1u << ((ig & 1) * 16 + src16);
+          for (int s_ = 8; s_ >= 1; s_ >>= 1) {
+            const uint32_t lo = s_ == 8 ? 0x00ffu : s_ == 4 ? 0x0f0fu : s_ == 2 ? 0x3333u : 0x5555u;
+            const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s_);
+            x = (l16 & s_) ? (((y >> s_) & lo) | (x & (lo << s_))) : ((x & lo) | ((y & lo) << s_));
           }
+          kb[ig >> 1] |= x << ((ig & 1) * 16);   // bit (row in the 64-row half) of this thread's key column
         }
       }
       if (warp % 4 == 0) FB_TR(wg, it, 0);

@@ -672,7 +672,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
         continue;
       }
       const int row = ti.m0 + t * kBM + r_in_tile;
-      // dropout (kDrop instantiation): the mask of common.h's dropout_keep -- one Philox-4x32-10 call per 16
+      // dropout (kDrop instantiation): the mask of common.h's dropout_keep -- one Philox-4x32-7 call per 16
       // consecutive columns of a row, a weight is kept iff its byte <= floor(255 * p_keep).  A thread owns a row, so
       // every 32-column chunk of P costs it two calls.  The row sum is taken BEFORE dropout and 1 / p_keep is folded
       // into the final normalisation (flash_fwd_kernel.h:399-409, softmax.h:381-447).
@@ -943,7 +943,7 @@ fwd_kernel(const __grid_constant__ Params p, const __grid_constant__ FwdTma tm_p
               if (i & 1) sumb = fadd2(sumb, pk2(p0, p1)); else suma = fadd2(suma, pk2(p0, p1));
               if constexpr (kDrop) {
                 if (i % 8 == 0)
-                  rnd = philox4x32_10(dctx.seed, dctx.row_base + (uint32_t)((blk.j * kBN + c * 32 + 2 * i) >> 4), dctx.offset);
+                  rnd = philox4x32_7(dctx.seed, dctx.row_base + (uint32_t)((blk.j * kBN + c * 32 + 2 * i) >> 4), dctx.offset);
                 const int e = (2 * i) & 15;                       // position of the pair inside its 16-column group
                 const uint32_t w = e < 4 ? rnd.x : e < 8 ? rnd.y : e < 12 ? rnd.z : rnd.w;
                 if (((w >> ((e & 3) * 8)) & 0xffu) > dctx.threshold) p0 = 0.f;

@@ -181,7 +181,7 @@ probs_kernel(const __grid_constant__ Params p, const __grid_constant__ ProbsTma 
           if constexpr (kDrop) {
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
-              const uint4 r = philox4x32_10(dc.seed, dc.row_base + (uint32_t)((col0 >> 4) + g), dc.offset);
+              const uint4 r = philox4x32_7(dc.seed, dc.row_base + (uint32_t)((col0 >> 4) + g), dc.offset);
               const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
               for (int i = 0; i < 16; ++i)

@@ -16,7 +16,7 @@ Behaviour kept from the reference:
   * packed inputs get one packed gradient tensor                                (:108-113,167-176)
 
 Dropout (``dropout_p > 0``) runs inside the tcgen05 forward / backward kernels for head dims up to 128 (generic SIMT
-kernels beyond) with a Philox-4x32-10 mask and the reference's 8-bit keep threshold
+kernels beyond) with a Philox-4x32-7 mask and the reference's 8-bit keep threshold
 (csrc/flash_attn/src/softmax.h:381-447); the random stream is this library's own (one Philox call per 16 columns of a
 row), so masks are reproducible from ``rng_state`` but not bit-identical to the reference's -- the reference's tests
 check dropout through ``S_dmask`` and the drop fraction, which is how tests/test_dropout_gpu.py checks it here.
@@ -112,11 +112,21 @@ def _prefer_expanded_heads(b, sk, h, h_k, device) -> bool:
     return eff(nkb * h * b) > eff(grouped) + 0.06
 
 
-def _new_rng_state():
-    """(seed, offset) for the Philox dropout mask, drawn from torch's CPU generator (reproducible under
-    ``torch.manual_seed``); kept as a small CPU tensor so that saving it for backward costs no device sync.  The
-    reference saves the CUDA generator's philox state the same way (csrc/flash_attn/flash_api.cpp:300-316)."""
-    return torch.randint(0, 2 ** 62, (2,), dtype=torch.int64)
+def _new_rng_state(device=None):
+    """(seed, offset) for the Philox dropout mask, as a small CPU tensor (saving it for backward costs no device sync).
+
+    Taken from the CUDA generator of the tensor's device like the reference does (csrc/flash_attn/flash_api.cpp:300-316):
+    seed = the generator's seed, offset = its current Philox offset, which is then advanced -- so ``torch.manual_seed`` /
+    ``torch.cuda.manual_seed`` reproduce a run and consecutive calls get different masks.  Falls back to torch's CPU
+    generator where the CUDA generator is not reachable."""
+    try:
+        idx = device.index if device is not None and device.index is not None else torch.cuda.current_device()
+        gen = torch.cuda.default_generators[idx]
+        seed, offset = int(gen.initial_seed()), int(gen.get_offset())
+        gen.set_offset(offset + 4)          # one (seed, offset) pair per launch; cuRAND's convention keeps offsets multiples of 4
+        return torch.tensor([seed & (2 ** 63 - 1), offset], dtype=torch.int64)
+    except Exception:  # noqa: BLE001
+        return torch.randint(0, 2 ** 62, (2,), dtype=torch.int64)
 
 
 def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softmax, mask: _Mask = _NO_MASK,
@@ -165,7 +175,7 @@ def _flash_attn_forward(q, k, v, dropout_p, softmax_scale, causal, return_softma
     _fill_mask(p, mask, b, sk, keep)
     rng_state = S_dmask = None
     if dropout_p > 0.0:
-        rng_state = _new_rng_state()
+        rng_state = _new_rng_state(q.device)
         p.p_dropout = dropout_p
         p.philox_seed, p.philox_offset = int(rng_state[0]), int(rng_state[1])
         if return_softmax:   # (b, h, sq_rounded, sk_rounded), probabilities negated where dropped (flash_api.cpp:276-279)
