@@ -46,7 +46,6 @@ constexpr int kTilesPerCta = 2;   // Q tiles per work tile
 constexpr int kStages = 4;        // K/V ring depth
 constexpr int kThreads = 384;     // 2 softmax warpgroups + {MMA warp, TMA warp, 2 idle warps} (register-budget warpgroup)
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 domain: P stays below 2^8
 
 struct FwdTma {

@@ -39,8 +39,6 @@ template <int HD> struct PL {
   static constexpr int kThreads = 192;
 };
 
-__device__ __forceinline__ int bcast0(int v) { return __shfl_sync(0xffffffffu, v, 0); }
-
 template <int HD, bool kBf16, bool kDrop>
 __global__ void __launch_bounds__(PL<HD>::kThreads, 1)
 probs_kernel(const __grid_constant__ Params p, const __grid_constant__ ProbsTma tm_param, const ProbsTma *__restrict__ tm_dev) {
