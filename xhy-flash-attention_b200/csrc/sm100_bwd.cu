@@ -475,6 +475,10 @@ bwd_kernel(const __grid_constant__ Params p, const __grid_constant__ BwdTma tm_p
       tc_fence_before();
       mbar_arrive(bar(BB_DQ_EMPTY));
       if (warp == 8) FB_TR(3, it, 2);
+      // Measured alternative (round 2): red.global.add.v4.f32 straight from the registers into the same tile, to spare the
+      // shared-memory traffic of the staging (64 KB in + 64 KB out per query block on top of ~380 KB of MMA operand reads,
+      // TMA writes and dS^T) -- 83 % SLOWER on C3: 16-byte reductions scattered over 32 rows per instruction are no match
+      // for the bulk unit's 16 KB reduce-adds.
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
         if (c < n_chunks) {
