@@ -962,7 +962,7 @@ void bwd_post_convert_dq(const Params &p, cudaStream_t s) {
 bool sm100_bwd_supported(const Params &p, std::string *why) {
   auto no = [&](const char *w) { if (why) *why = w; return false; };
   if (p.d > 128 && !sm100_bwd_wide_eligible(p))
-    return no("head_size > 128 together with FlashMask / dropout / attn_mask / softcap / deterministic");
+    return no("head_size > 128 together with FlashMask / attn_mask / softcap / deterministic");
   if (!p.dq_accum) return no("no dq_accum workspace");
   if (p.d_rounded != round_up(p.d, 32) || p.seqlen_q_rounded % kB != 0 || p.seqlen_q_rounded < p.seqlen_q)
     return no("rounded sizes are not the documented ones");

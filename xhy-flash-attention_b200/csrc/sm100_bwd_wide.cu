@@ -23,7 +23,7 @@
 // TMEM columns: S^T/P^T [0,64)  dP^T/dS^T [64,128)  dQ^T [128,192)  dV [256,384)  dK [384,512).
 //
 // Features: causal (both alignments), sliding window, varlen, seqused, GQA/MQA, per-q-head dK/dV (dkv_expanded),
-// bf16/fp16.  FlashMask / dropout / dense mask / softcap / deterministic with d > 128 stay on the generic kernels.
+// bf16/fp16, dropout (kDrop).  FlashMask / dense mask / softcap / deterministic with d > 128 stay on the generic kernels.
 #include <math_constants.h>
 #include <type_traits>
 
@@ -122,7 +122,7 @@ __device__ __forceinline__ int64_t wide_acc_tile(const Params &p, const WTile &t
   return (int64_t)t.acc_tile0 + (int64_t)hq * t.acc_tiles_per_head + (m >> 1);
 }
 
-template <bool kBf16>
+template <bool kBf16, bool kDrop>
 __global__ void __launch_bounds__(kWThreads, 1)
 bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma tm_param, const WTma *__restrict__ tm_dev) {
   using L = WSmem;
@@ -345,6 +345,7 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
     const uint32_t ds_row_a = sbase + L::kDS + r * 128;
     const int shift = t.sk - t.sq;
     const int shiftc = p.causal_bottom_right ? shift : 0;
+    const float rp_drop = kDrop ? 1.f / (1.f - p.p_dropout) : 1.f;
     const uint32_t lse2_a = sbase + L::kVec + (wg * 32) * 4;
     const uint32_t dpsum_a = sbase + L::kVec + (kBQ + wg * 32) * 4;
     for (int it = 0; it < n_it; ++it) {
@@ -359,6 +360,32 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
         int vlo, vhi;
         visible_rows(mc, col, vlo, vhi);
         mbits = outside_bits(vlo, vhi, m0 + wg * 32);
+      }
+      // Dropout (kDrop): keep bits of this thread's 32 (query, key) pairs -- the scheme of sm100_bwd.cu: a lane runs the
+      // generator for one query row of a 16-row group and the 16 key columns of its half warp, turns the 16 bytes into a
+      // 16-bit keep mask, and the half warp transposes the 16 x 16 bit matrix with four butterfly shuffles.
+      uint32_t kb = 0xffffffffu;
+      if constexpr (kDrop) {
+        kb = 0u;
+        const int l16 = lane & 15;
+        const uint32_t thr4 = (uint32_t)floorf((1.f - p.p_dropout) * 255.f) * 0x01010101u;
+        const uint64_t ncg = (uint64_t)((p.seqlen_k + 15) / 16);
+        const uint64_t cg = (uint64_t)((t.n0 + (warp % 4) * 32 + (lane & 16)) >> 4);
+        const uint64_t head_base = ((uint64_t)t.bi * p.h + hq) * (uint64_t)p.seqlen_q;
+        auto keep4 = [&](uint32_t w) { return ((__vcmpleu4(w, thr4) & 0x08040201u) * 0x01010101u) >> 24; };
+#pragma unroll
+        for (int ig = 0; ig < 2; ++ig) {
+          const uint64_t rrow = (uint64_t)(m0 + wg * 32 + ig * 16 + l16);
+          const uint4 rnd = philox4x32_7(p.philox_seed, (head_base + rrow) * ncg + cg, p.philox_offset);
+          uint32_t x = keep4(rnd.x) | (keep4(rnd.y) << 4) | (keep4(rnd.z) << 8) | (keep4(rnd.w) << 12);
+#pragma unroll
+          for (int s_ = 8; s_ >= 1; s_ >>= 1) {
+            const uint32_t lo = s_ == 8 ? 0x00ffu : s_ == 4 ? 0x0f0fu : s_ == 2 ? 0x3333u : 0x5555u;
+            const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s_);
+            x = (l16 & s_) ? (((y >> s_) & lo) | (x & (lo << s_))) : ((x & lo) | ((y & lo) << s_));
+          }
+          kb |= x << (ig * 16);
+        }
       }
       mbar_wait(bar(WB_Q_FULL), it & 1);     // LSE / dPsum rows of this query block are in smem
       mbar_wait(bar(WB_S_FULL), it & 1);
@@ -382,8 +409,14 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
             if ((mbits >> i) & 1u) pr[i] = 0.f;
         }
         uint32_t pk[16];
+        if constexpr (kDrop) {   // dV sees the dropped weights (1 / p_keep is applied to dV in the epilogue)
 #pragma unroll
-        for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[2 * i], pr[2 * i + 1]);
+          for (int i = 0; i < 16; ++i)
+            pk[i] = pack2<kBf16>(((kb >> (2 * i)) & 1u) ? pr[2 * i] : 0.f, ((kb >> (2 * i + 1)) & 1u) ? pr[2 * i + 1] : 0.f);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = pack2<kBf16>(pr[2 * i], pr[2 * i + 1]);
+        }
         tmem_st16(tP, pk);
       }
       tmem_wait_st();
@@ -401,10 +434,18 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           const float4 d4 = lds128(dpsum_a + i * 4);
-          const float e0 = pr[i + 0] * (__uint_as_float(dp[i + 0]) - d4.x);
-          const float e1 = pr[i + 1] * (__uint_as_float(dp[i + 1]) - d4.y);
-          const float e2 = pr[i + 2] * (__uint_as_float(dp[i + 2]) - d4.z);
-          const float e3 = pr[i + 3] * (__uint_as_float(dp[i + 3]) - d4.w);
+          float g0 = __uint_as_float(dp[i + 0]), g1 = __uint_as_float(dp[i + 1]), g2 = __uint_as_float(dp[i + 2]),
+                g3 = __uint_as_float(dp[i + 3]);
+          if constexpr (kDrop) {   // dP = keep / p_keep * (dO . V)
+            g0 = ((kb >> (i + 0)) & 1u) ? g0 * rp_drop : 0.f;
+            g1 = ((kb >> (i + 1)) & 1u) ? g1 * rp_drop : 0.f;
+            g2 = ((kb >> (i + 2)) & 1u) ? g2 * rp_drop : 0.f;
+            g3 = ((kb >> (i + 3)) & 1u) ? g3 * rp_drop : 0.f;
+          }
+          const float e0 = pr[i + 0] * (g0 - d4.x);
+          const float e1 = pr[i + 1] * (g1 - d4.y);
+          const float e2 = pr[i + 2] * (g2 - d4.z);
+          const float e3 = pr[i + 3] * (g3 - d4.w);
           pk[i / 2] = pack2<kBf16>(e0, e1);
           pk[i / 2 + 1] = pack2<kBf16>(e2, e3);
         }
@@ -431,7 +472,7 @@ bwd_wide_kernel(const __grid_constant__ Params p, const __grid_constant__ WTma t
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
       T *dst = which == 0 ? dv_row : dk_row;
-      const float mul = which == 0 ? 1.f : p.softmax_scale;
+      const float mul = which == 0 ? rp_drop : p.softmax_scale;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
@@ -481,7 +522,7 @@ TmaDesc4 wdesc(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batc
   return x;
 }
 
-template <bool kBf16> void launch_wide(const Params &p, cudaStream_t s) {
+template <bool kBf16, bool kDrop> void launch_wide(const Params &p, cudaStream_t s) {
   using L = WSmem;
   const bool packed = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool dev_rows = packed && (p.total_q < 0 || p.total_k < 0);
@@ -499,7 +540,7 @@ template <bool kBf16> void launch_wide(const Params &p, cudaStream_t s) {
     tm_dev = reinterpret_cast<WTma *>(patch_tma_rows(&tm.q, k_like, 4, p.cu_seqlens_q, p.cu_seqlens_k, p.b, s));
   }
   bwd_pre_dpsum(p, s);
-  auto kern = bwd_wide_kernel<kBf16>;
+  auto kern = bwd_wide_kernel<kBf16, kDrop>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kTotal, smem_set);
   dim3 grid(2 * ceil_div(p.seqlen_k, kBK), p.dkv_expanded ? p.h : p.h_k, p.b);
@@ -516,12 +557,14 @@ template <bool kBf16> void launch_wide(const Params &p, cudaStream_t s) {
 }  // namespace
 
 bool sm100_bwd_wide_eligible(const Params &p) {
-  return p.d > 128 && p.d <= 256 && p.lt_start == nullptr && p.p_dropout == 0.f && p.attn_mask == nullptr &&
-         p.softcap == 0.f && !p.deterministic;
+  return p.d > 128 && p.d <= 256 && p.lt_start == nullptr && p.attn_mask == nullptr && p.softcap == 0.f &&
+         !p.deterministic;
 }
 
 void sm100_bwd_wide(const Params &p, cudaStream_t s) {
-  if (p.is_bf16) launch_wide<true>(p, s); else launch_wide<false>(p, s);
+  const bool drop = p.p_dropout > 0.f;
+  if (p.is_bf16) { if (drop) launch_wide<true, true>(p, s); else launch_wide<true, false>(p, s); }
+  else { if (drop) launch_wide<false, true>(p, s); else launch_wide<false, false>(p, s); }
 }
 
 }  // namespace fa

@@ -1126,7 +1126,7 @@ bool sm100_fwd_supported(const Params &p, std::string *why) {
       return no("output not 16-byte aligned");
     return true;
   }
-  if (p.d > 128 && !sm100_fwd2_eligible(p)) return no("head_size > 128 together with FlashMask / dropout / attn_mask / softcap");
+  if (p.d > 128 && !sm100_fwd2_eligible(p)) return no("head_size > 128 together with FlashMask / attn_mask / softcap");
   if (p.num_splits > 1) return no("split-KV");
   if (p.attn_mask && (p.lt_start || p.p_dropout > 0.f)) return no("dense attn_mask together with FlashMask / dropout");
   if (p.softcap > 0.f && (p.lt_start || p.p_dropout > 0.f || p.attn_mask)) return no("softcap together with FlashMask / dropout / attn_mask");

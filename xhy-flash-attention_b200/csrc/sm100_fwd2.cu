@@ -164,7 +164,7 @@ __device__ __forceinline__ float exp2_poly(float x) {
   return __int_as_float(__float_as_int(q) + (__float_as_int(jm) << 23));
 }
 
-template <int HD, bool kBf16, int QT, int EB>
+template <int HD, bool kBf16, int QT, int EB, bool kDrop>
 __global__ void __launch_bounds__(F2<HD, QT, EB>::kThreads, 1)
 fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm_param, const Fwd2Tma *__restrict__ tm_dev,
             int num_m, int num_tiles) {
@@ -473,6 +473,11 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
         scale_log2 = scale_nat * kLog2e;
       }
       float m_ref = -CUDART_INF_F, l = 0.f;
+      // dropout (kDrop): the mask of common.h's dropout_keep -- one Philox call per 16 consecutive columns of a row; this
+      // thread's 64 columns of a key block are four calls.  Row sum before dropout, 1 / p_keep folded into the
+      // normalisation (flash_fwd_kernel.h:399-409, softmax.h:381-447), as in sm100_fwd.cu.
+      DropCtx dctx;
+      if constexpr (kDrop) { dctx = make_drop_ctx(p, ti.bi, ti.hq, row); out_scale = 1.f / (1.f - p.p_dropout); }
       const int nb_total = ti.n_hi[t] - ti.n_lo[t];
       for (int nb = 0; nb < nb_total; ++nb, ++g) {
         const int j = ti.n_lo[t] + nb;
@@ -550,6 +555,8 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t pk[16];
+          uint4 km = make_uint4(0, 0, 0, 0);
+          (void)km;
           float pprev0 = 0.f, pprev1 = 0.f;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
@@ -568,6 +575,16 @@ fwd2_kernel(const __grid_constant__ Params p, const __grid_constant__ Fwd2Tma tm
               else { pprev0 = p0; pprev1 = p1; }
             } else {
               pk[i] = pack2<kBf16>(p0, p1);
+              if constexpr (kDrop) {   // keep mask on the packed pair: byte-wise compare, widened by a byte permute
+                if (i % 8 == 0) {
+                  const uint4 r4 = philox4x32_7(dctx.seed, dctx.row_base + (uint32_t)((c0 + c * 32 + 2 * i) >> 4), dctx.offset);
+                  const uint32_t thr4 = dctx.threshold * 0x01010101u;
+                  km = make_uint4(__vcmpleu4(r4.x, thr4), __vcmpleu4(r4.y, thr4), __vcmpleu4(r4.z, thr4), __vcmpleu4(r4.w, thr4));
+                }
+                const int e = (2 * i) & 15;
+                const uint32_t w = e < 4 ? km.x : e < 8 ? km.y : e < 12 ? km.z : km.w;
+                pk[i] &= __byte_perm(w, 0u, (e & 3) == 0 ? 0x1100u : 0x3322u);
+              }
             }
           }
           if constexpr (!kFp8) tmem_st16(tP + c * 16, pk);
@@ -667,7 +684,7 @@ TmaDesc4 desc2(const fa_b200_tensor &t, int d, int heads, int64_t rows, int batc
   return x;
 }
 
-template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2> void launch_fwd2(const Params &p, cudaStream_t s) {
+template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2, bool kDrop = false> void launch_fwd2(const Params &p, cudaStream_t s) {
   using L = F2<HD, QT, EB>;
   const bool packed_q = p.cu_seqlens_q && !p.varlen_padded_input;
   const bool packed_k = p.cu_seqlens_k && !p.varlen_padded_input;
@@ -687,7 +704,7 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2> void lau
   }
   const int num_m = ceil_div(p.seqlen_q, kBM * L::kQT);
   const int num_tiles = p.b * p.h * num_m;
-  auto kern = fwd2_kernel<HD, kBf16, QT, EB>;
+  auto kern = fwd2_kernel<HD, kBf16, QT, EB, kDrop>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
   const int grid = std::min(num_tiles, device_sm_count());
@@ -705,7 +722,8 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2> void lau
 // The split-row forward serves calls without FlashMask / dropout / dense mask / softcap (those keep the one-thread-per-row
 // kernel of sm100_fwd.cu, head dims <= 128 only).
 bool sm100_fwd2_eligible(const Params &p) {
-  return p.lt_start == nullptr && p.p_dropout == 0.f && p.attn_mask == nullptr && p.softcap == 0.f;
+  // dropout: instantiated for head dims above 128 only (below, sm100_fwd.cu has its own kDrop instantiations)
+  return p.lt_start == nullptr && (p.p_dropout == 0.f || (p.d > 128 && !p.is_e4m3)) && p.attn_mask == nullptr && p.softcap == 0.f;
 }
 
 // FP8 (e4m3) forward: same kernel with byte operands, tcgen05.mma kind::f8f6f4 (twice the 16-bit rate), P rounded to
@@ -725,6 +743,10 @@ void sm100_fwd2(const Params &p, cudaStream_t s) {
   }
   if (p.d <= 64) { if (p.is_bf16) launch_fwd2<64, true>(p, s); else launch_fwd2<64, false>(p, s); }
   else if (p.d <= 128) { if (p.is_bf16) launch_fwd2<128, true>(p, s); else launch_fwd2<128, false>(p, s); }
+  else if (p.p_dropout > 0.f) {   // head dims above 128 with dropout
+    if (p.d <= 192) { if (p.is_bf16) launch_fwd2<192, true, 1, 2, true>(p, s); else launch_fwd2<192, false, 1, 2, true>(p, s); }
+    else { if (p.is_bf16) launch_fwd2<256, true, 1, 2, true>(p, s); else launch_fwd2<256, false, 1, 2, true>(p, s); }
+  }
   else if (p.d <= 192) { if (p.is_bf16) launch_fwd2<192, true>(p, s); else launch_fwd2<192, false>(p, s); }
   else { if (p.is_bf16) launch_fwd2<256, true>(p, s); else launch_fwd2<256, false>(p, s); }
 }
