@@ -29,7 +29,8 @@ struct ProbsTma { CUtensorMap q, k; };
 
 template <int HD> struct PL {
   static constexpr int kTileBytes = 128 * HD * 2;
-  static constexpr int kStages = HD <= 128 ? 3 : 2;
+  // two CTAs per SM (2 x 256 TMEM columns, <= 113 KB of shared memory each): the epilogue of one covers the S = Q K^T of the other
+  static constexpr int kStages = HD <= 64 ? 3 : 2;   // (head dims above 128: 192 KB, one CTA per SM as before)
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kTileBytes;
   static constexpr int kBarOff = kKOff + kStages * kTileBytes;
@@ -40,7 +41,7 @@ template <int HD> struct PL {
 };
 
 template <int HD, bool kBf16, bool kDrop>
-__global__ void __launch_bounds__(PL<HD>::kThreads, 1)
+__global__ void __launch_bounds__(PL<HD>::kThreads, 2)
 probs_kernel(const __grid_constant__ Params p, const __grid_constant__ ProbsTma tm_param, const ProbsTma *__restrict__ tm_dev) {
   using L = PL<HD>;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
