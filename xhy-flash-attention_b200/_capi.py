@@ -103,6 +103,8 @@ def load() -> C.CDLL:
     lib.fa_b200_prepare_num_splits.restype = C.c_bool
     lib.fa_b200_abi_version.restype = C.c_int
     lib.fa_b200_last_kernel_kind.restype = C.c_int
+    lib.fa_b200_set_forward_sm_reserve.argtypes = [C.c_int]
+    lib.fa_b200_set_forward_sm_reserve.restype = None
     lib.fa_b200_launch_count.argtypes = [C.c_int]
     lib.fa_b200_launch_count.restype = C.c_int64
     lib.fa_b200_last_fallback_reason.restype = C.c_char_p

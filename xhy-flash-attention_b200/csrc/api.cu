@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <vector>
@@ -18,6 +19,7 @@ namespace fa {
 
 static thread_local std::unique_ptr<char[]> tls_error;
 static thread_local int tls_last_kind = 0;
+static thread_local int tls_fwd_reserve = 0;   // fa_b200_set_forward_sm_reserve
 static std::atomic<int64_t> g_launches{0};  // process-wide: backward runs on autograd worker threads
 
 void note_launch(int kind) {
@@ -78,6 +80,7 @@ static DevInfo dev_info() {
   return d;
 }
 int device_sm_count() { return dev_info().sm_count; }
+int forward_grid_sms() { return std::max(1, dev_info().sm_count - tls_fwd_reserve); }
 int device_cc_major() { return dev_info().cc_major; }
 
 static void check_common(const Params &p) {
@@ -225,6 +228,7 @@ float fa_b200_profile_last_ms(int slot) {
 
 int fa_b200_abi_version(void) { return FA_B200_ABI_VERSION; }
 int fa_b200_last_kernel_kind(void) { return fa::tls_last_kind; }
+void fa_b200_set_forward_sm_reserve(int num_sms) { fa::tls_fwd_reserve = num_sms > 0 ? num_sms : 0; }
 int64_t fa_b200_launch_count(int reset) {
   int64_t v = reset ? fa::g_launches.exchange(0) : fa::g_launches.load();
   return v;

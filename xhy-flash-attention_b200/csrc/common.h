@@ -38,6 +38,8 @@ int device_sm_count();
 // optional per-kernel timing (fa_b200_profile_*): slot 0 = forward kernel, slot 1 = backward main kernel
 void profile_mark(int slot, bool begin, cudaStream_t s);
 int device_cc_major();
+// CTAs of a persistent forward launch: every SM, minus what the calling thread reserved with fa_b200_set_forward_sm_reserve
+int forward_grid_sms();
 
 // dispatchers (api.cu)
 void run_fwd(const Params &p, cudaStream_t s);

@@ -1088,7 +1088,7 @@ template <int HD, bool kBf16, bool kFM, bool kDrop, bool kMask = false, bool kCa
   auto kern = fwd_kernel<HD, kBf16, kFM, kDrop, kMask, kCap>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
-  const int grid = std::min(num_tiles, device_sm_count());
+  const int grid = std::min(num_tiles, kFM ? device_sm_count() : forward_grid_sms());
   int *counter = nullptr;                          // stream-ordered scratch: the dynamic scheduler's tile counter
   if (kFM) {
     FA_CUDA(cudaMallocAsync(&counter, sizeof(int), s));

@@ -707,7 +707,7 @@ template <int HD, bool kBf16, int QT = (HD <= 128 ? 2 : 1), int EB = 2, bool kDr
   auto kern = fwd2_kernel<HD, kBf16, QT, EB, kDrop>;
   static std::atomic<bool> smem_set[64];
   ensure_dynamic_smem(kern, L::kDynBytes, smem_set);
-  const int grid = std::min(num_tiles, device_sm_count());
+  const int grid = std::min(num_tiles, forward_grid_sms());
   profile_mark(0, true, s);
   kern<<<grid, L::kThreads, L::kDynBytes, s>>>(p, tm, tm_dev, num_m, num_tiles);
   profile_mark(0, false, s);

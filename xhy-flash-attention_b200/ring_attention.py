@@ -26,6 +26,7 @@ library is missing.
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Optional, Tuple
 
 import torch
@@ -112,6 +113,7 @@ _CUDA_OPS = RingOps()
 # ----------------------------------------------------------------------------------------------------
 # communication: one rotation of a list of tensors to rank+1, received from rank-1
 # ----------------------------------------------------------------------------------------------------
+RESERVE_SMS = int(os.environ.get("FA_B200_RING_RESERVE_SMS", "8"))   # SMs left to NCCL during the ring forward (0 = none)
 STALL_TRACE = None     # set to a list to collect (tag, event before, event after) around every wait for a transfer
 
 
@@ -209,6 +211,28 @@ def ring_forward(q, k, v, softmax_scale, causal, group=None, ops: RingOps = _CUD
     lse_acc = torch.full((b, s, h), float("inf"), dtype=torch.float32, device=q.device)   # +inf = nothing merged yet
     comm = _comm_stream(q)
     k_cur, v_cur = k.contiguous(), v.contiguous()
+    # While a K/V block travels, NCCL's send / recv kernels hold a few SMs.  The forward kernel is persistent (one CTA per
+    # SM, tile list cut statically): the CTAs that find their SM taken start late and the launch ends late by as much --
+    # measured on 8 GPUs as 9 % of the step with the compute stream never waiting for data (tools/ring_trace.py).  Leaving
+    # those SMs free costs the forward RESERVE_SMS / 148 of its throughput and removes the delay (70.2 -> 67.3 ms).
+    # Worth it while the lost throughput (RESERVE_SMS / 148 of a step's forward, ~1 PFLOP/s) is below the delay it avoids
+    # (one K/V block at ~250 GB/s): blocks up to ~32k tokens per rank at 32 / 8 heads of 128.
+    reserve = 0
+    if ops.exchange and world > 1 and q.is_cuda and ops.block_fwd is _cuda_block_fwd and RESERVE_SMS > 0:
+        t_fwd = 4.0 * b * s * (s / 2) * h * d / 1.0e15
+        t_xfer = 2.0 * k.numel() * k.element_size() / 2.5e11
+        if RESERVE_SMS / 148.0 * t_fwd < t_xfer:
+            reserve = RESERVE_SMS
+    if reserve:
+        _capi.load().fa_b200_set_forward_sm_reserve(reserve)
+    try:
+        return _ring_forward_steps(q, k_cur, v_cur, o_acc, lse_acc, comm, softmax_scale, causal, group, ops, world, rank)
+    finally:
+        if reserve:
+            _capi.load().fa_b200_set_forward_sm_reserve(0)
+
+
+def _ring_forward_steps(q, k_cur, v_cur, o_acc, lse_acc, comm, softmax_scale, causal, group, ops, world, rank):
     for t in range(world):
         rot = _Rotation(group, [k_cur, v_cur], comm, ops.exchange, f"fwd kv {t}") if t + 1 < world else None
         src = (rank - t) % world
